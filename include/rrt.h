@@ -1,0 +1,232 @@
+/*
+ * rrt.h — C ABI of the B200-native renderer that replaces the per-pixel hot path of
+ * conor722/rust-ray-tracer (primary-ray generation -> octree traversal -> Moller-Trumbore
+ * -> textured / normal-mapped shading with shadow and mirror rays).
+ *
+ * The reference has no FFI of its own; the seam these entry points replace is
+ *     Scene::draw_scene(&mut self, rt: RayTracer)            src/scene/engine.rs:186-255
+ * called once from main()                                     src/main.rs:74
+ * and, per ray, RayTracer::get_ray_colour(origin, direction)  src/scene/raytracer.rs:29-31.
+ *
+ * Everything is plain C: caller-owned pointers + sizes, no torch / C++ types.
+ * All scene arithmetic is IEEE f64 (the reference's Vector3d is f64, src/scene/engine.rs:9-14).
+ * All functions return RRT_OK (0) or a negative rrt_status; rrt_last_error() gives the text.
+ * Nothing here ever falls back to a CPU renderer: without a CUDA device the render calls fail
+ * with RRT_ERR_CUDA.
+ */
+#ifndef RRT_H_
+#define RRT_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RRT_ABI_VERSION 1
+#define RRT_MAX_LIGHTS 16
+
+typedef enum rrt_status {
+    RRT_OK = 0,
+    RRT_ERR_INVALID = -1,   /* bad argument / malformed scene (reference would panic)      */
+    RRT_ERR_CUDA = -2,      /* CUDA runtime error, or no device                             */
+    RRT_ERR_IO = -3,        /* file could not be read (loader)                              */
+    RRT_ERR_PARSE = -4,     /* .obj / .mtl syntax the reference's parser would panic on     */
+    RRT_ERR_DEPTH = -5,     /* octree deeper than RRT_MAX_OCTREE_DEPTH (reference: unbounded)*/
+    RRT_ERR_NOMEM = -6
+} rrt_status;
+
+/* ---- scene description (inputs of RayTracer / SceneData, src/scene/raytracer.rs:22-26,
+ *      src/scene/scenedata.rs:6-13).  Borrowed for the duration of rrt_scene_create only. ---- */
+
+/* Texture { colours: Vec<Color>, width, height }  src/scene/entities.rs:87-91.
+ * rgb = packed RGB8, row-major, 3*width*height bytes (src/file_management/utils.rs:353-361). */
+typedef struct rrt_texture {
+    int32_t width;
+    int32_t height;
+    const uint8_t* rgb;
+} rrt_texture;
+
+/* Material  src/scene/material.rs:11-22 (Ka, Kd, Ks, Ns, texture, bump_map, reflectivity). */
+typedef struct rrt_material {
+    double ka[3];
+    double kd[3];
+    double ks[3];
+    double ns;        /* specular_weight; -1.0 disables the specular term (raytracer.rs:288) */
+    double kr;        /* reflectivity in [0,1]                                               */
+    int32_t tex_id;   /* index into textures[]; required (utils.rs:61)                       */
+    int32_t bump_id;  /* index into textures[] or -1 (Option<Arc<Texture>>)                  */
+} rrt_material;
+
+/* Triangles in `f`-line order (== octree.triangles order, src/collision/octree.rs:45-47);
+ * that index is what hit-id planes report. */
+typedef struct rrt_scene_desc {
+    uint64_t n_tris;
+    const double* v;            /* n_tris x 9 : v1.xyz v2.xyz v3.xyz      (entities.rs:75-77) */
+    const double* vt;           /* n_tris x 6 : (x,y) of v1,v2,v3 tex     (entities.rs:78-80) */
+    const double* vn;           /* n_tris x 9 : v1,v2,v3 normals          (entities.rs:81-83) */
+    const int32_t* material_id; /* n_tris     : index into materials[]                         */
+    uint32_t n_materials;
+    const rrt_material* materials;
+    uint32_t n_textures;
+    const rrt_texture* textures;
+    double root_min[3];         /* octree root box; reference hard-codes -20 (utils.rs:145)    */
+    double root_max[3];         /* ... and +20                                                  */
+} rrt_scene_desc;
+
+/* Light enum  src/scene/entities.rs:5-9 */
+enum { RRT_LIGHT_AMBIENT = 0, RRT_LIGHT_POINT = 1, RRT_LIGHT_DIRECTIONAL = 2 };
+typedef struct rrt_light {
+    int32_t kind;
+    int32_t _pad;
+    double intensity;
+    double vec[3];   /* position (point) / direction (directional) / unused (ambient) */
+} rrt_light;
+
+/* Per-frame parameters: the constants main() hard-codes (src/main.rs:14-15,32-66), the Viewport
+ * (src/scene/engine.rs:106-120) and raytracer.rs:17,20.  rrt_render_params_default() fills the
+ * reference's values. */
+typedef struct rrt_render_params {
+    int32_t width;             /* canvas width  (main.rs:14)                         */
+    int32_t height;            /* canvas height (main.rs:15)                         */
+    double origin[3];          /* RayTracer.origin (main.rs:62-66)                   */
+    double viewport[3];        /* width, height, distance = 1,1,1 (engine.rs:113-119)*/
+    int32_t n_lights;
+    int32_t max_depth;         /* MAX_REFLECTION_DEPTH = 5 (raytracer.rs:20)         */
+    rrt_light lights[RRT_MAX_LIGHTS];
+    double surface_offset;     /* SURFACE_OFFSET = 1e-4 (raytracer.rs:17)            */
+    /* Extension (the reference has no camera rotation): if use_camera_rot != 0 the
+     * primary direction is camera_rot (row-major 3x3) * (x*xs, y*ys, z). 0 => bit-exact reference. */
+    int32_t use_camera_rot;
+    int32_t _pad;
+    double camera_rot[9];
+} rrt_render_params;
+
+/* Row sharding for multi-GPU: buffer rows are grouped in tile rows of `tile_rows`
+ * scan-lines; tile row j belongs to shard (j % n_shards).  n_shards = 1 => whole frame. */
+typedef struct rrt_shard {
+    int32_t tile_rows;
+    int32_t n_shards;
+    int32_t shard_index;
+} rrt_shard;
+
+/* Octree / traversal statistics (structure that src/collision/octree.rs:41-241 produced). */
+typedef struct rrt_scene_stats {
+    uint64_t n_tris;           /* triangles given                                   */
+    uint64_t n_tris_stored;    /* triangles that landed in some node list           */
+    uint64_t n_tris_dropped;   /* AABB misses the root box (octree.rs:71-73)        */
+    uint64_t n_nodes;          /* reference node count (incl. empty)                */
+    uint64_t n_nodes_nonempty; /* nodes with triangle_count > 0 (kept on device)    */
+    uint64_t max_depth;
+    uint64_t root_list;        /* triangles owned by the root                       */
+    uint64_t max_list;         /* longest non-root node list                        */
+    uint64_t n_cull_nodes;     /* nodes of the per-list culling hierarchies         */
+    uint64_t device_bytes;     /* bytes resident in HBM for this scene              */
+} rrt_scene_stats;
+
+/* Per-frame work counters summed over all rays (optional; see rrt_render_counters). */
+typedef struct rrt_counters {
+    uint64_t rays_primary;
+    uint64_t rays_shadow;
+    uint64_t rays_reflect;
+    uint64_t mt_tests;      /* exact Moller-Trumbore evaluations started  */
+    uint64_t box_tests;     /* child-octant slab tests (ray.rs:135-144)   */
+    uint64_t cull_tests;    /* culling-hierarchy box tests                */
+    uint64_t nodes_entered; /* non-empty octree nodes entered             */
+} rrt_counters;
+
+typedef struct rrt_scene rrt_scene;   /* opaque: owns the device copy of the flattened scene */
+
+/* ---- library ---- */
+int rrt_abi_version(void);
+const char* rrt_last_error(void);            /* thread-local, never NULL */
+int rrt_device_count(void);                  /* number of CUDA devices, 0 if none / no driver */
+
+/* ---- parameters ---- */
+/* Fills width/height 800x800, camera (0,2,-10), the four lights of src/main.rs:32-58,
+ * viewport 1,1,1, max_depth 5, surface_offset 1e-4, identity camera. */
+void rrt_render_params_default(rrt_render_params* p);
+
+/* ---- scene lifetime (replaces: RayTracer moved into draw_scene, engine.rs:186-187) ---- */
+/* Builds the reference octree on the host by exact sequential insertion
+ * (src/collision/octree.rs:41-241, src/collision/aabb.rs:25-60), flattens it, uploads to `device`. */
+int rrt_scene_create(const rrt_scene_desc* desc, int device, rrt_scene** out);
+void rrt_scene_destroy(rrt_scene* scene);
+int rrt_scene_get_stats(const rrt_scene* scene, rrt_scene_stats* out);
+
+/* ---- rendering (replaces Scene::draw_scene, engine.rs:186-255) ---- */
+/* Host-buffer call: fb_0rgb[width*height] receives the reference canvas layout
+ * (0x00RRGGBB, row-major, top row first, row 0 left zero: engine.rs:146-158, entities.rs:32-36).
+ * hit_ids (may be NULL): int32[height][width][4], depth-0 hit triangle per supersample in the order
+ * d1..d4 of engine.rs:207-236, -1 = miss / row 0.  device_ms (may be NULL) = kernel time (CUDA events).
+ * Synchronous; includes the device->host copy. */
+int rrt_render(rrt_scene* scene, const rrt_render_params* params,
+               uint32_t* fb_0rgb, int32_t* hit_ids, float* device_ms);
+
+/* Device-buffer call: same result written to device memory of the scene's device, enqueued on
+ * `cuda_stream` (a cudaStream_t cast to void*, NULL = default stream); does not synchronise.
+ * With n_shards > 1 only the owned rows are rendered and written COMPACTLY: owned row k (in
+ * increasing buffer-row order) goes to d_fb[k*width ...]; see rrt_shard_rows(). */
+int rrt_render_device(rrt_scene* scene, const rrt_render_params* params, const rrt_shard* shard,
+                      uint32_t* d_fb, int32_t* d_hit_ids, void* cuda_stream);
+
+/* Number of buffer rows shard `shard_index` owns for a frame of `height` rows (row 0 included). */
+int rrt_shard_rows(int32_t height, const rrt_shard* shard);
+
+/* Scatter gathered compact shards back to a full frame: d_gathered = n_shards blocks of
+ * `rows_per_block` rows each (block s = shard s, padded), d_fb = full frame.  Row 0 is zeroed. */
+int rrt_deinterleave_device(int device, const uint32_t* d_gathered, int32_t rows_per_block,
+                            int32_t width, int32_t height, int32_t tile_rows, int32_t n_shards,
+                            uint32_t* d_fb, void* cuda_stream);
+
+/* Per-ray seam (RayTracer::get_ray_colour, raytracer.rs:29-31; Ray::intersect_with_octant_with_max_t,
+ * ray.rs:104-168).  Host arrays: origins/dirs n x 3, max_t n (NULL = +inf).
+ * rrt_trace_rays: out_tri n (int32, -1 miss), out_tuv n x 3 (t,u,v; untouched on miss).
+ * rrt_ray_colours: out_rgb n x 3 (u8). */
+int rrt_trace_rays(rrt_scene* scene, uint64_t n, const double* origins, const double* dirs,
+                   const double* max_t, int32_t* out_tri, double* out_tuv);
+int rrt_ray_colours(rrt_scene* scene, const rrt_render_params* params, uint64_t n,
+                    const double* origins, const double* dirs, uint8_t* out_rgb);
+
+/* Render one frame with work counters enabled (slower instrumented kernel). fb may be NULL. */
+int rrt_render_counters(rrt_scene* scene, const rrt_render_params* params,
+                        uint32_t* fb_0rgb, rrt_counters* out);
+
+/* ---- host-side octree (src/collision/octree.rs) exposed for inspection / tests; no GPU needed ---- */
+typedef struct rrt_octree rrt_octree;
+int rrt_octree_build(const double* v /* n x 9 */, uint64_t n_tris,
+                     const double root_min[3], const double root_max[3], rrt_octree** out);
+void rrt_octree_destroy(rrt_octree* t);
+uint64_t rrt_octree_node_count(const rrt_octree* t);
+/* For node i: box (6 doubles min.xyz max.xyz), triangle_count (octree.rs:11), first child index
+ * (0 = leaf; children are 8 consecutive nodes, octree.rs:226-237), list length. */
+int rrt_octree_node(const rrt_octree* t, uint64_t i, double box[6], uint64_t* triangle_count,
+                    uint64_t* first_child, uint64_t* list_len);
+/* Copies node i's triangle list (insertion order, octree.rs:78,91,103) into out[0..cap). Returns length. */
+int64_t rrt_octree_node_list(const rrt_octree* t, uint64_t i, uint32_t* out, uint64_t cap);
+
+/* ---- loaders (src/file_management/utils.rs:22-343), host only ---- */
+/* Parsed scene owned by the library. Textures are NOT decoded here: the caller decodes the files
+ * named by rrt_obj_texture_name() (the reference uses the `image` crate, utils.rs:345-368). */
+typedef struct rrt_obj rrt_obj;
+int rrt_obj_load(const char* obj_path, const char* base_dir /* for mtllib; NULL = cwd */, rrt_obj** out);
+void rrt_obj_destroy(rrt_obj* o);
+uint64_t rrt_obj_n_tris(const rrt_obj* o);
+const double* rrt_obj_v(const rrt_obj* o);
+const double* rrt_obj_vt(const rrt_obj* o);
+const double* rrt_obj_vn(const rrt_obj* o);
+const int32_t* rrt_obj_material_id(const rrt_obj* o);
+uint32_t rrt_obj_n_materials(const rrt_obj* o);
+const rrt_material* rrt_obj_materials(const rrt_obj* o);   /* tex_id / bump_id index texture names */
+const char* rrt_obj_material_name(const rrt_obj* o, uint32_t i);
+uint32_t rrt_obj_n_textures(const rrt_obj* o);
+const char* rrt_obj_texture_name(const rrt_obj* o, uint32_t i);
+
+/* ---- headless output (stands in for the minifb window, engine.rs:122-167) ---- */
+int rrt_write_ppm(const char* path, const uint32_t* fb_0rgb, int32_t width, int32_t height);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RRT_H_ */
