@@ -1,0 +1,429 @@
+// rrt_api.cu — the C ABI of include/rrt.h: scene upload, render calls, per-ray seams.
+// No CPU rendering path exists in this library: every render entry point needs a CUDA device.
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "../../include/rrt.h"
+#include "rrt_octree.h"
+#include "rrt_render.h"
+#include "rrt_shade.cuh"
+
+using namespace rrt;
+
+namespace {
+
+thread_local std::string g_err = "";
+
+int fail(int code, const std::string& msg) {
+    g_err = msg;
+    return code;
+}
+int cuda_fail(cudaError_t e, const char* what) {
+    return fail(RRT_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+}
+#define CU(x)                                                    \
+    do {                                                         \
+        cudaError_t e_ = (x);                                    \
+        if (e_ != cudaSuccess) return cuda_fail(e_, #x);         \
+    } while (0)
+
+// lists longer than this get a culling hierarchy; RRT_CULL_THRESHOLD=0 scans every list linearly
+uint32_t cull_threshold() {
+    const char* s = std::getenv("RRT_CULL_THRESHOLD");
+    if (s && *s) return (uint32_t)std::strtoul(s, nullptr, 10);
+    return 8;
+}
+
+}  // namespace
+
+struct rrt_scene {
+    int device = 0;
+    DevScene dev{};
+    rrt_scene_stats stats{};
+    std::vector<void*> allocs;
+    // scratch for the host-buffer entry points, grown on demand
+    uint32_t* d_fb = nullptr;
+    int32_t* d_hit = nullptr;
+    size_t fb_cap = 0, hit_cap = 0;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+
+    template <class T>
+    int upload(const T* host, size_t n, const T** out) {
+        void* p = nullptr;
+        const size_t bytes = std::max<size_t>(n, 1) * sizeof(T);
+        CU(cudaMalloc(&p, bytes));
+        allocs.push_back(p);
+        if (n) CU(cudaMemcpy(p, host, n * sizeof(T), cudaMemcpyHostToDevice));
+        stats.device_bytes += bytes;
+        *out = static_cast<const T*>(p);
+        return RRT_OK;
+    }
+    ~rrt_scene() {
+        cudaSetDevice(device);
+        for (void* p : allocs) cudaFree(p);
+        if (d_fb) cudaFree(d_fb);
+        if (d_hit) cudaFree(d_hit);
+        if (ev0) cudaEventDestroy(ev0);
+        if (ev1) cudaEventDestroy(ev1);
+    }
+};
+
+namespace {
+
+int make_params(const rrt_render_params* p, const rrt_shard* sh, DevParams* out) {
+    if (!p) return fail(RRT_ERR_INVALID, "null params");
+    if (p->width <= 0 || p->height <= 0) return fail(RRT_ERR_INVALID, "width/height must be positive");
+    if ((int64_t)p->width * p->height > (int64_t)1 << 30) return fail(RRT_ERR_INVALID, "frame too large");
+    if (p->n_lights < 0 || p->n_lights > RRT_MAX_LIGHTS) return fail(RRT_ERR_INVALID, "n_lights out of range");
+    if (p->max_depth < 0) return fail(RRT_ERR_INVALID, "max_depth < 0");
+    DevParams d{};
+    d.W = p->width;
+    d.H = p->height;
+    d.ox = p->origin[0]; d.oy = p->origin[1]; d.oz = p->origin[2];
+    d.xs = p->viewport[0] / (double)p->width;    // engine.rs:189
+    d.ys = p->viewport[1] / (double)p->height;   // engine.rs:190
+    d.zv = p->viewport[2];                       // engine.rs:191
+    d.n_lights = p->n_lights;
+    d.max_depth = p->max_depth > kMaxReflectDepth ? kMaxReflectDepth : p->max_depth;
+    for (int i = 0; i < p->n_lights; ++i) {
+        if (p->lights[i].kind < 0 || p->lights[i].kind > 2) return fail(RRT_ERR_INVALID, "bad light kind");
+        d.lights[i] = p->lights[i];
+    }
+    d.offset = p->surface_offset;
+    d.use_rot = p->use_camera_rot;
+    for (int i = 0; i < 9; ++i) d.rot[i] = p->camera_rot[i];
+    rrt_shard one{1, 1, 0};
+    if (!sh) sh = &one;
+    if (sh->tile_rows < 1 || sh->n_shards < 1 || sh->shard_index < 0 || sh->shard_index >= sh->n_shards)
+        return fail(RRT_ERR_INVALID, "bad shard");
+    d.tile_rows = sh->tile_rows;
+    d.n_shards = sh->n_shards;
+    d.shard_index = sh->shard_index;
+    d.n_rows_local = rrt_shard_rows(p->height, sh);
+    *out = d;
+    return RRT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int rrt_abi_version(void) { return RRT_ABI_VERSION; }
+void rrt_set_last_error_(const char* msg) { g_err = msg ? msg : ""; }  // used by rrt_loader.cpp
+const char* rrt_last_error(void) { return g_err.c_str(); }
+
+int rrt_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+void rrt_render_params_default(rrt_render_params* p) {
+    if (!p) return;
+    std::memset(p, 0, sizeof *p);
+    p->width = 800;   // main.rs:14
+    p->height = 800;  // main.rs:15
+    p->origin[0] = 0.0; p->origin[1] = 2.0; p->origin[2] = -10.0;  // main.rs:62-66
+    p->viewport[0] = p->viewport[1] = p->viewport[2] = 1.0;        // engine.rs:113-119
+    p->n_lights = 4;                                               // main.rs:32-58
+    p->lights[0] = rrt_light{RRT_LIGHT_AMBIENT, 0, 0.5, {0, 0, 0}};
+    p->lights[1] = rrt_light{RRT_LIGHT_POINT, 0, 0.4, {-7.0, 1.0, -15.0}};
+    p->lights[2] = rrt_light{RRT_LIGHT_POINT, 0, 0.5, {0.0, 1.0, -41.0}};
+    p->lights[3] = rrt_light{RRT_LIGHT_DIRECTIONAL, 0, 0.4, {-5.0, 0.0, 20.0}};
+    p->max_depth = 5;           // raytracer.rs:20
+    p->surface_offset = 0.0001; // raytracer.rs:17
+    p->use_camera_rot = 0;
+    p->camera_rot[0] = p->camera_rot[4] = p->camera_rot[8] = 1.0;
+}
+
+int rrt_shard_rows(int32_t height, const rrt_shard* sh) {
+    if (!sh || sh->n_shards <= 1) return height;
+    const int T = sh->tile_rows, G = sh->n_shards, s = sh->shard_index;
+    if (T < 1 || s < 0 || s >= G) return 0;
+    int rows = 0;
+    for (int j = s; (int64_t)j * T < height; j += G) rows += std::min(T, height - j * T);
+    return rows;
+}
+
+int rrt_scene_create(const rrt_scene_desc* d, int device, rrt_scene** out) {
+    if (!d || !out) return fail(RRT_ERR_INVALID, "null argument");
+    *out = nullptr;
+    if (d->n_tris > 0x7FFFFFF0ull) return fail(RRT_ERR_INVALID, "too many triangles");
+    if (d->n_tris && (!d->v || !d->vt || !d->vn || !d->material_id)) return fail(RRT_ERR_INVALID, "null triangle arrays");
+    // validation the reference performs by panicking (utils.rs:61 unwrap; Vec index out of range)
+    for (uint32_t i = 0; i < d->n_textures; ++i)
+        if (d->textures[i].width <= 0 || d->textures[i].height <= 0 || !d->textures[i].rgb)
+            return fail(RRT_ERR_INVALID, "empty texture");
+    for (uint32_t i = 0; i < d->n_materials; ++i) {
+        const rrt_material& m = d->materials[i];
+        if (m.tex_id < 0 || (uint32_t)m.tex_id >= d->n_textures) return fail(RRT_ERR_INVALID, "material without texture (utils.rs:61)");
+        if (m.bump_id >= (int32_t)d->n_textures) return fail(RRT_ERR_INVALID, "bump_id out of range");
+        if (m.bump_id >= 0) {
+            const rrt_texture &a = d->textures[m.tex_id], &b = d->textures[m.bump_id];
+            // the bump map is indexed with the COLOUR map's (tx,ty) and its own stride (raytracer.rs:128)
+            if ((int64_t)b.width * (a.height - 1) + (a.width - 1) >= (int64_t)b.width * b.height)
+                return fail(RRT_ERR_INVALID, "bump map smaller than colour map (reference would panic)");
+        }
+    }
+    for (uint64_t i = 0; i < d->n_tris; ++i)
+        if (d->material_id[i] < 0 || (uint32_t)d->material_id[i] >= d->n_materials)
+            return fail(RRT_ERR_INVALID, "material_id out of range");
+    int ndev = rrt_device_count();
+    if (ndev <= 0) return fail(RRT_ERR_CUDA, "no CUDA device (this library has no CPU fallback)");
+    if (device < 0 || device >= ndev) return fail(RRT_ERR_INVALID, "device index out of range");
+    CU(cudaSetDevice(device));
+
+    // host: exact reference octree, then flatten
+    HostOctree tree;
+    std::string err;
+    if (!tree.build(d->v, d->n_tris, d->root_min, d->root_max, &err)) return fail(RRT_ERR_DEPTH, err);
+    FlatScene flat;
+    flatten(tree, d->v, cull_threshold(), &flat);
+
+    auto sc = std::make_unique<rrt_scene>();
+    sc->device = device;
+    rrt_scene_stats& st = sc->stats;
+    st.n_tris = d->n_tris;
+    st.n_tris_stored = flat.n_stored;
+    st.n_tris_dropped = tree.n_dropped;
+    st.n_nodes = tree.nodes.size();
+    st.n_nodes_nonempty = (tree.nodes[0].triangle_count > 0) ? flat.nodes.size() : 0;
+    st.max_depth = tree.max_depth;
+    st.root_list = flat.root_list;
+    st.max_list = flat.max_list;
+    st.n_cull_nodes = flat.cull.size();
+    { std::vector<HostNode>().swap(tree.nodes); std::vector<uint32_t>().swap(tree.next); }
+
+    int rc;
+    if ((rc = sc->upload(flat.nodes.data(), flat.nodes.size(), &sc->dev.nodes))) return rc;
+    if ((rc = sc->upload(flat.tris.data(), flat.tris.size(), &sc->dev.tris))) return rc;
+    if ((rc = sc->upload(flat.cull.data(), flat.cull.size(), &sc->dev.cull))) return rc;
+    sc->dev.n_nodes = (uint32_t)flat.nodes.size();
+    sc->dev.root_tri_count = st.n_tris_stored ? 1u : 0u;
+
+    // shading records by original triangle id (entities.rs:78-84)
+    {
+        std::vector<DevShade> sh(d->n_tris);
+        for (uint64_t i = 0; i < d->n_tris; ++i) {
+            const double *n = d->vn + 9 * i, *t = d->vt + 6 * i;
+            DevShade& s = sh[i];
+            std::memcpy(s.n1, n, 24); std::memcpy(s.n2, n + 3, 24); std::memcpy(s.n3, n + 6, 24);
+            std::memcpy(s.t1, t, 16); std::memcpy(s.t2, t + 2, 16); std::memcpy(s.t3, t + 4, 16);
+            s.material = d->material_id[i];
+            s._pad = 0;
+        }
+        if ((rc = sc->upload(sh.data(), sh.size(), &sc->dev.shade))) return rc;
+    }
+    {
+        std::vector<DevMaterial> ms(d->n_materials);
+        for (uint32_t i = 0; i < d->n_materials; ++i) {
+            const rrt_material& m = d->materials[i];
+            std::memcpy(ms[i].ka, m.ka, 24); std::memcpy(ms[i].kd, m.kd, 24); std::memcpy(ms[i].ks, m.ks, 24);
+            ms[i].ns = m.ns; ms[i].kr = m.kr; ms[i].tex = m.tex_id; ms[i].bump = m.bump_id;
+        }
+        if ((rc = sc->upload(ms.data(), ms.size(), &sc->dev.materials))) return rc;
+    }
+    {
+        std::vector<DevTexture> ts(d->n_textures);
+        std::vector<uchar4> tmp;
+        for (uint32_t i = 0; i < d->n_textures; ++i) {
+            const rrt_texture& t = d->textures[i];
+            const size_t n = (size_t)t.width * t.height;
+            tmp.resize(n);
+            for (size_t k = 0; k < n; ++k) tmp[k] = make_uchar4(t.rgb[3 * k], t.rgb[3 * k + 1], t.rgb[3 * k + 2], 0);
+            const uchar4* dp = nullptr;
+            if ((rc = sc->upload(tmp.data(), n, &dp))) return rc;
+            ts[i] = DevTexture{dp, (uint32_t)t.width, (uint32_t)t.height};
+        }
+        if ((rc = sc->upload(ts.data(), ts.size(), &sc->dev.tex))) return rc;
+    }
+    CU(cudaEventCreate(&sc->ev0));
+    CU(cudaEventCreate(&sc->ev1));
+    *out = sc.release();
+    return RRT_OK;
+}
+
+void rrt_scene_destroy(rrt_scene* s) { delete s; }
+
+int rrt_scene_get_stats(const rrt_scene* s, rrt_scene_stats* out) {
+    if (!s || !out) return fail(RRT_ERR_INVALID, "null argument");
+    *out = s->stats;
+    return RRT_OK;
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------- render entry points
+namespace {
+
+template <class T>
+int ensure(T** p, size_t* cap, size_t n) {
+    if (*cap >= n) return RRT_OK;
+    if (*p) cudaFree(*p);
+    *p = nullptr;
+    *cap = 0;
+    CU(cudaMalloc((void**)p, n * sizeof(T)));
+    *cap = n;
+    return RRT_OK;
+}
+
+struct DevBuf {  // RAII scratch for the per-ray seams
+    void* p = nullptr;
+    ~DevBuf() { if (p) cudaFree(p); }
+    int alloc(size_t bytes) {
+        CU(cudaMalloc(&p, bytes ? bytes : 1));
+        return RRT_OK;
+    }
+};
+
+}  // namespace
+
+extern "C" {
+
+int rrt_render_device(rrt_scene* s, const rrt_render_params* p, const rrt_shard* shard, uint32_t* d_fb,
+                      int32_t* d_hit_ids, void* cuda_stream) {
+    if (!s || !d_fb) return fail(RRT_ERR_INVALID, "null argument");
+    DevParams P;
+    int rc = make_params(p, shard, &P);
+    if (rc) return rc;
+    CU(cudaSetDevice(s->device));
+    CU(launch_render(s->dev, P, d_fb, d_hit_ids, nullptr, (cudaStream_t)cuda_stream));
+    return RRT_OK;
+}
+
+int rrt_render(rrt_scene* s, const rrt_render_params* p, uint32_t* fb, int32_t* hit_ids, float* device_ms) {
+    if (!s || !fb) return fail(RRT_ERR_INVALID, "null argument");
+    DevParams P;
+    int rc = make_params(p, nullptr, &P);
+    if (rc) return rc;
+    CU(cudaSetDevice(s->device));
+    const size_t n = (size_t)P.W * P.H;
+    if ((rc = ensure(&s->d_fb, &s->fb_cap, n))) return rc;
+    if (hit_ids && (rc = ensure(&s->d_hit, &s->hit_cap, n * 4))) return rc;
+    CU(cudaEventRecord(s->ev0, 0));
+    CU(launch_render(s->dev, P, s->d_fb, hit_ids ? s->d_hit : nullptr, nullptr, 0));
+    CU(cudaEventRecord(s->ev1, 0));
+    CU(cudaMemcpy(fb, s->d_fb, n * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+    if (hit_ids) CU(cudaMemcpy(hit_ids, s->d_hit, n * 4 * sizeof(int32_t), cudaMemcpyDeviceToHost));
+    if (device_ms) CU(cudaEventElapsedTime(device_ms, s->ev0, s->ev1));
+    return RRT_OK;
+}
+
+int rrt_render_counters(rrt_scene* s, const rrt_render_params* p, uint32_t* fb, rrt_counters* out) {
+    if (!s || !out) return fail(RRT_ERR_INVALID, "null argument");
+    DevParams P;
+    int rc = make_params(p, nullptr, &P);
+    if (rc) return rc;
+    CU(cudaSetDevice(s->device));
+    const size_t n = (size_t)P.W * P.H;
+    if ((rc = ensure(&s->d_fb, &s->fb_cap, n))) return rc;
+    DevBuf c;
+    if ((rc = c.alloc(sizeof(DevCounters)))) return rc;
+    CU(cudaMemset(c.p, 0, sizeof(DevCounters)));
+    CU(launch_render(s->dev, P, s->d_fb, nullptr, (DevCounters*)c.p, 0));
+    DevCounters h;
+    CU(cudaMemcpy(&h, c.p, sizeof h, cudaMemcpyDeviceToHost));
+    if (fb) CU(cudaMemcpy(fb, s->d_fb, n * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+    out->rays_primary = h.rays_primary; out->rays_shadow = h.rays_shadow; out->rays_reflect = h.rays_reflect;
+    out->mt_tests = h.mt_tests; out->box_tests = h.box_tests; out->cull_tests = h.cull_tests;
+    out->nodes_entered = h.nodes_entered;
+    return RRT_OK;
+}
+
+int rrt_deinterleave_device(int device, const uint32_t* d_gathered, int32_t rows_per_block, int32_t width,
+                            int32_t height, int32_t tile_rows, int32_t n_shards, uint32_t* d_fb, void* cuda_stream) {
+    if (!d_gathered || !d_fb) return fail(RRT_ERR_INVALID, "null argument");
+    if (width <= 0 || height <= 0 || tile_rows < 1 || n_shards < 1 || rows_per_block < 1)
+        return fail(RRT_ERR_INVALID, "bad geometry");
+    CU(cudaSetDevice(device));
+    CU(launch_deinterleave(d_gathered, rows_per_block, width, height, tile_rows, n_shards, d_fb, (cudaStream_t)cuda_stream));
+    return RRT_OK;
+}
+
+int rrt_trace_rays(rrt_scene* s, uint64_t n, const double* o, const double* d, const double* max_t, int32_t* out_tri,
+                   double* out_tuv) {
+    if (!s || (n && (!o || !d || !out_tri))) return fail(RRT_ERR_INVALID, "null argument");
+    if (n == 0) return RRT_OK;
+    CU(cudaSetDevice(s->device));
+    DevBuf bo, bd, bm, bt, buv;
+    int rc;
+    if ((rc = bo.alloc(n * 24)) || (rc = bd.alloc(n * 24)) || (rc = bt.alloc(n * 4)) || (rc = buv.alloc(n * 24))) return rc;
+    if (max_t && (rc = bm.alloc(n * 8))) return rc;
+    CU(cudaMemcpy(bo.p, o, n * 24, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(bd.p, d, n * 24, cudaMemcpyHostToDevice));
+    if (max_t) CU(cudaMemcpy(bm.p, max_t, n * 8, cudaMemcpyHostToDevice));
+    CU(cudaMemset(buv.p, 0, n * 24));
+    CU(launch_trace(s->dev, n, (const double*)bo.p, (const double*)bd.p, max_t ? (const double*)bm.p : nullptr,
+                    (int32_t*)bt.p, (double*)buv.p, 0));
+    CU(cudaMemcpy(out_tri, bt.p, n * 4, cudaMemcpyDeviceToHost));
+    if (out_tuv) {
+        // "untouched on miss": copy through a staging vector and merge
+        std::vector<double> tmp(3 * n);
+        CU(cudaMemcpy(tmp.data(), buv.p, n * 24, cudaMemcpyDeviceToHost));
+        for (uint64_t i = 0; i < n; ++i)
+            if (out_tri[i] >= 0) std::memcpy(out_tuv + 3 * i, tmp.data() + 3 * i, 24);
+    }
+    return RRT_OK;
+}
+
+int rrt_ray_colours(rrt_scene* s, const rrt_render_params* p, uint64_t n, const double* o, const double* d,
+                    uint8_t* out_rgb) {
+    if (!s || (n && (!o || !d || !out_rgb))) return fail(RRT_ERR_INVALID, "null argument");
+    DevParams P;
+    int rc = make_params(p, nullptr, &P);
+    if (rc) return rc;
+    if (n == 0) return RRT_OK;
+    CU(cudaSetDevice(s->device));
+    DevBuf bo, bd, bc;
+    if ((rc = bo.alloc(n * 24)) || (rc = bd.alloc(n * 24)) || (rc = bc.alloc(n * 3))) return rc;
+    CU(cudaMemcpy(bo.p, o, n * 24, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(bd.p, d, n * 24, cudaMemcpyHostToDevice));
+    CU(launch_colours(s->dev, P, n, (const double*)bo.p, (const double*)bd.p, (uint8_t*)bc.p, 0));
+    CU(cudaMemcpy(out_rgb, bc.p, n * 3, cudaMemcpyDeviceToHost));
+    return RRT_OK;
+}
+
+// ---------------------------------------------------------------- host octree inspection (no GPU)
+struct rrt_octree {
+    HostOctree t;
+};
+
+int rrt_octree_build(const double* v, uint64_t n_tris, const double root_min[3], const double root_max[3],
+                     rrt_octree** out) {
+    if (!out || (n_tris && !v) || !root_min || !root_max) return fail(RRT_ERR_INVALID, "null argument");
+    if (n_tris > 0x7FFFFFF0ull) return fail(RRT_ERR_INVALID, "too many triangles");
+    auto t = std::make_unique<rrt_octree>();
+    std::string err;
+    if (!t->t.build(v, n_tris, root_min, root_max, &err)) return fail(RRT_ERR_DEPTH, err);
+    *out = t.release();
+    return RRT_OK;
+}
+void rrt_octree_destroy(rrt_octree* t) { delete t; }
+uint64_t rrt_octree_node_count(const rrt_octree* t) { return t ? t->t.nodes.size() : 0; }
+int rrt_octree_node(const rrt_octree* t, uint64_t i, double box[6], uint64_t* triangle_count, uint64_t* first_child,
+                    uint64_t* list_len) {
+    if (!t || i >= t->t.nodes.size()) return fail(RRT_ERR_INVALID, "node index out of range");
+    const HostNode& n = t->t.nodes[i];
+    if (box) std::memcpy(box, n.box, sizeof n.box);
+    if (triangle_count) *triangle_count = n.triangle_count;
+    if (first_child) *first_child = n.first_child;
+    if (list_len) *list_len = n.list_len;
+    return RRT_OK;
+}
+int64_t rrt_octree_node_list(const rrt_octree* t, uint64_t i, uint32_t* out, uint64_t cap) {
+    if (!t || i >= t->t.nodes.size()) return -1;
+    uint64_t k = 0;
+    for (uint32_t tr = t->t.nodes[i].head; tr != UINT32_MAX; tr = t->t.next[tr], ++k)
+        if (out && k < cap) out[k] = tr;
+    return (int64_t)k;
+}
+
+}  // extern "C"

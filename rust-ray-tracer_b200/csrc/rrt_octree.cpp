@@ -1,0 +1,331 @@
+// rrt_octree.cpp — exact host replay of the reference's incremental octree construction
+// (src/collision/octree.rs:41-241, src/collision/aabb.rs:25-60) on flat arrays, plus flattening into
+// the device layout (rrt_octree.h).  The tree SHAPE is part of the results contract: it decides which
+// triangle wins a t-tie and which triangles a ray can reach at all.
+#include "rrt_octree.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <numeric>
+
+namespace rrt {
+
+namespace {
+
+// aabb.rs:49-60 — closed-interval overlap, a = [amin,amax], b likewise (6 doubles min.xyz max.xyz)
+inline bool boxes_overlap(const double* a, const double* b) {
+    if (a[3] < b[0] || a[0] > b[3]) return false;
+    if (a[4] < b[1] || a[1] > b[4]) return false;
+    if (a[5] < b[2] || a[2] > b[5]) return false;
+    return true;
+}
+
+// aabb.rs:25-47 — Rust f64::min/max ignore a NaN operand, exactly like fmin/fmax.
+inline void tri_box(const double* v, double* b) {
+    for (int k = 0; k < 3; ++k) {
+        b[k] = std::fmin(v[k], std::fmin(v[3 + k], v[6 + k]));
+        b[3 + k] = std::fmax(v[k], std::fmax(v[3 + k], v[6 + k]));
+    }
+}
+
+}  // namespace
+
+bool HostOctree::build(const double* v, uint64_t n, const double root_min[3], const double root_max[3],
+                       std::string* err) {
+    nodes.clear();
+    next.assign(n, UINT32_MAX);
+    n_tris = n;
+    n_dropped = 0;
+    max_depth = 0;
+    HostNode root;
+    for (int k = 0; k < 3; ++k) {
+        root.box[k] = root_min[k];
+        root.box[3 + k] = root_max[k];
+    }
+    nodes.push_back(root);  // octree.rs:23-39
+    nodes.reserve(n / 2 + 16);
+
+    auto append = [&](uint32_t node, uint32_t tri) {  // self.nodes[i].triangles.push(tri)
+        HostNode& nd = nodes[node];
+        if (nd.tail == UINT32_MAX)
+            nd.head = tri;
+        else
+            next[nd.tail] = tri;
+        nd.tail = tri;
+        nd.list_len++;
+    };
+
+    for (uint64_t i = 0; i < n; ++i) {
+        double tb[6];
+        tri_box(v + 9 * i, tb);
+        uint32_t node = 0;
+        // push_at_octant (octree.rs:54-108) with the tail recursion unrolled into a loop.
+        for (;;) {
+            if (!boxes_overlap(tb, nodes[node].box)) {  // octree.rs:65,71-73 (only ever false at the root)
+                if (node == 0) n_dropped++;
+                break;
+            }
+            nodes[node].triangle_count += 1;  // octree.rs:75
+            const bool leaf = nodes[node].first_child == 0;
+            if (leaf && nodes[node].list_len == 0) {  // octree.rs:77-78: first triangle in an empty leaf stays
+                append(node, (uint32_t)i);
+                break;
+            }
+            if (leaf) {  // octree.rs:79-80 -> subdivide (octree.rs:121-241)
+                if (nodes[node].depth + 1 > (uint32_t)kMaxOctreeDepth) {
+                    if (err) *err = "octree deeper than kMaxOctreeDepth (coincident triangles?)";
+                    return false;
+                }
+                const HostNode p = nodes[node];
+                const double x0 = p.box[0], y0 = p.box[1], z0 = p.box[2];
+                const double x1 = p.box[3], y1 = p.box[4], z1 = p.box[5];
+                const double xm = x0 + (x1 - x0) / 2.0;  // octree.rs:136,142
+                const double ym = y0 + (y1 - y0) / 2.0;  // octree.rs:137,144
+                const double zm = z0 + (z1 - z0) / 2.0;  // octree.rs:138,146
+                const uint32_t first = (uint32_t)nodes.size();
+                // octree.rs:216-225: bbl, bfl, bfr, bbr, tbl, tfl, tfr, tbr (x-high for k in {2,3,6,7},
+                // y-high for k >= 4, z-high for k in {1,2,5,6})
+                for (int k = 0; k < 8; ++k) {
+                    const bool xh = (k == 2 || k == 3 || k == 6 || k == 7), yh = k >= 4,
+                               zh = (k == 1 || k == 2 || k == 5 || k == 6);
+                    HostNode c;
+                    c.box[0] = xh ? xm : x0;
+                    c.box[3] = xh ? x1 : xm;
+                    c.box[1] = yh ? ym : y0;
+                    c.box[4] = yh ? y1 : ym;
+                    c.box[2] = zh ? zm : z0;
+                    c.box[5] = zh ? z1 : zm;
+                    c.depth = p.depth + 1;
+                    nodes.push_back(c);
+                }
+                nodes[node].first_child = first;
+                max_depth = std::max(max_depth, p.depth + 1);
+            }
+            // octree.rs:82-104: descend iff exactly one child box overlaps the triangle box
+            const uint32_t fc = nodes[node].first_child;
+            int hits = 0;
+            uint32_t only = 0;
+            for (int k = 0; k < 8; ++k)
+                if (boxes_overlap(nodes[fc + k].box, tb)) {
+                    hits++;
+                    only = fc + k;
+                }
+            if (hits == 1) {
+                node = only;
+                continue;
+            }
+            append(node, (uint32_t)i);
+            break;
+        }
+    }
+    return true;
+}
+
+void HostOctree::list_of(uint32_t node, std::vector<uint32_t>* out) const {
+    out->clear();
+    for (uint32_t t = nodes[node].head; t != UINT32_MAX; t = next[t]) out->push_back(t);
+}
+
+// ---------------------------------------------------------------- culling hierarchy (per long list)
+namespace {
+
+struct CullBuilder {
+    const double* v;
+    std::vector<uint32_t>& ids;       // triangle ids of this list, permuted in place into leaf order
+    std::vector<double> boxes;        // per entry of ids (parallel array), 6 doubles
+    std::vector<DevCull>& out;
+    uint32_t rec_base;                // record index of ids[0]
+    static constexpr uint32_t kLeaf = 4;
+
+    static void pad_box(double* b) {
+        for (int k = 0; k < 3; ++k) {
+            const double m = std::fmax(std::fabs(b[k]), std::fabs(b[3 + k]));
+            const double p = 1e-7 * std::fmax(1.0, m);
+            b[k] -= p;
+            b[3 + k] += p;
+        }
+    }
+    void bounds(uint32_t lo, uint32_t hi, double* b) const {
+        for (int k = 0; k < 3; ++k) { b[k] = INFINITY; b[3 + k] = -INFINITY; }
+        for (uint32_t i = lo; i < hi; ++i)
+            for (int k = 0; k < 3; ++k) {
+                b[k] = std::fmin(b[k], boxes[6 * (size_t)i + k]);
+                b[3 + k] = std::fmax(b[3 + k], boxes[6 * (size_t)i + 3 + k]);
+            }
+    }
+    static double area(const double* b) {
+        const double dx = b[3] - b[0], dy = b[4] - b[1], dz = b[5] - b[2];
+        return dx * dy + dy * dz + dz * dx;
+    }
+    // Partition [lo,hi) by a binned surface-area heuristic on centroids; returns mid.
+    uint32_t split(uint32_t lo, uint32_t hi) {
+        double cb[6];
+        for (int k = 0; k < 3; ++k) { cb[k] = INFINITY; cb[3 + k] = -INFINITY; }
+        auto cen = [&](uint32_t i, int k) { return 0.5 * (boxes[6 * (size_t)i + k] + boxes[6 * (size_t)i + 3 + k]); };
+        for (uint32_t i = lo; i < hi; ++i)
+            for (int k = 0; k < 3; ++k) {
+                cb[k] = std::fmin(cb[k], cen(i, k));
+                cb[3 + k] = std::fmax(cb[3 + k], cen(i, k));
+            }
+        constexpr int NB = 16;
+        double best_cost = INFINITY;
+        int best_axis = -1, best_bin = 0;
+        for (int ax = 0; ax < 3; ++ax) {
+            const double ext = cb[3 + ax] - cb[ax];
+            if (!(ext > 0.0)) continue;
+            double bb[NB][6];
+            uint32_t cnt[NB] = {0};
+            for (int b = 0; b < NB; ++b)
+                for (int k = 0; k < 3; ++k) { bb[b][k] = INFINITY; bb[b][3 + k] = -INFINITY; }
+            for (uint32_t i = lo; i < hi; ++i) {
+                int b = (int)((cen(i, ax) - cb[ax]) / ext * NB);
+                b = std::min(NB - 1, std::max(0, b));
+                cnt[b]++;
+                for (int k = 0; k < 3; ++k) {
+                    bb[b][k] = std::fmin(bb[b][k], boxes[6 * (size_t)i + k]);
+                    bb[b][3 + k] = std::fmax(bb[b][3 + k], boxes[6 * (size_t)i + 3 + k]);
+                }
+            }
+            double la[NB], ra[NB];
+            uint32_t lc[NB], rc[NB];
+            double acc[6];
+            for (int k = 0; k < 3; ++k) { acc[k] = INFINITY; acc[3 + k] = -INFINITY; }
+            uint32_t c = 0;
+            for (int b = 0; b < NB; ++b) {
+                for (int k = 0; k < 3; ++k) { acc[k] = std::fmin(acc[k], bb[b][k]); acc[3 + k] = std::fmax(acc[3 + k], bb[b][3 + k]); }
+                c += cnt[b];
+                la[b] = c ? area(acc) : 0.0;
+                lc[b] = c;
+            }
+            for (int k = 0; k < 3; ++k) { acc[k] = INFINITY; acc[3 + k] = -INFINITY; }
+            c = 0;
+            for (int b = NB - 1; b >= 0; --b) {
+                for (int k = 0; k < 3; ++k) { acc[k] = std::fmin(acc[k], bb[b][k]); acc[3 + k] = std::fmax(acc[3 + k], bb[b][3 + k]); }
+                c += cnt[b];
+                ra[b] = c ? area(acc) : 0.0;
+                rc[b] = c;
+            }
+            for (int b = 0; b + 1 < NB; ++b) {
+                if (lc[b] == 0 || rc[b + 1] == 0) continue;
+                const double cost = la[b] * lc[b] + ra[b + 1] * rc[b + 1];
+                if (cost < best_cost) { best_cost = cost; best_axis = ax; best_bin = b; }
+            }
+        }
+        if (best_axis < 0) return lo + (hi - lo) / 2;  // all centroids coincide: split by count
+        const double ext = cb[3 + best_axis] - cb[best_axis];
+        // in-place partition of ids+boxes
+        uint32_t i = lo, j = hi;
+        while (i < j) {
+            int b = (int)((cen(i, best_axis) - cb[best_axis]) / ext * NB);
+            b = std::min(NB - 1, std::max(0, b));
+            if (b <= best_bin) {
+                ++i;
+            } else {
+                --j;
+                std::swap(ids[i], ids[j]);
+                for (int k = 0; k < 6; ++k) std::swap(boxes[6 * (size_t)i + k], boxes[6 * (size_t)j + k]);
+            }
+        }
+        if (i == lo || i == hi) return lo + (hi - lo) / 2;
+        return i;
+    }
+    // Builds the subtree over [lo,hi) (hi-lo > kLeaf) and returns its DevCull index.
+    uint32_t build(uint32_t lo, uint32_t hi) {
+        const uint32_t me = (uint32_t)out.size();
+        out.emplace_back();
+        const uint32_t mid = split(lo, hi);
+        const uint32_t r[3] = {lo, mid, hi};
+        for (int s = 0; s < 2; ++s) {
+            double b[6];
+            bounds(r[s], r[s + 1], b);
+            pad_box(b);
+            const uint32_t n = r[s + 1] - r[s];
+            uint32_t child, count;
+            if (n <= kLeaf) {
+                child = 0x80000000u | (rec_base + r[s]);
+                count = n;
+            } else {
+                child = build(r[s], r[s + 1]);
+                count = 0;
+            }
+            DevCull& c = out[me];  // re-fetch: vector may have grown
+            std::memcpy(c.box[s], b, sizeof b);
+            c.child[s] = child;
+            c.count[s] = count;
+        }
+        return me;
+    }
+};
+
+}  // namespace
+
+void flatten(const HostOctree& t, const double* v, uint32_t cull_threshold, FlatScene* out) {
+    out->nodes.clear();
+    out->tris.clear();
+    out->cull.clear();
+    out->n_stored = out->root_list = out->max_list = 0;
+    out->max_depth = t.max_depth;
+    if (t.nodes.empty() || t.nodes[0].triangle_count == 0) {
+        // ray.rs:112-114: an empty root returns None for every ray; keep one inert node.
+        DevNode n{};
+        n.cull_root = UINT32_MAX;
+        out->nodes.push_back(n);
+        return;
+    }
+    // breadth-first renumbering of kept (triangle_count > 0) nodes; siblings stay consecutive
+    std::vector<uint32_t> order;  // device index -> host index
+    order.push_back(0);
+    out->nodes.emplace_back();
+    for (size_t d = 0; d < order.size(); ++d) {
+        const HostNode& h = t.nodes[order[d]];
+        DevNode dn{};
+        dn.cull_root = UINT32_MAX;
+        if (h.first_child != 0) {
+            const HostNode* c = &t.nodes[h.first_child];
+            // planes exactly as subdivide() produced them: child 0 = (min .. min+half), child 6 = (min+half .. max)
+            dn.px[0] = c[0].box[0]; dn.px[1] = c[0].box[3]; dn.px[2] = c[6].box[3];
+            dn.py[0] = c[0].box[1]; dn.py[1] = c[0].box[4]; dn.py[2] = c[6].box[4];
+            dn.pz[0] = c[0].box[2]; dn.pz[1] = c[0].box[5]; dn.pz[2] = c[6].box[5];
+            dn.first_child = (uint32_t)order.size();
+            for (int k = 0; k < 8; ++k)
+                if (c[k].triangle_count > 0) {
+                    dn.child_mask |= 1u << k;
+                    order.push_back(h.first_child + k);
+                    out->nodes.emplace_back();
+                }
+        }
+        out->nodes[d] = dn;
+    }
+    // triangle records, node by node
+    std::vector<uint32_t> ids;
+    for (size_t d = 0; d < order.size(); ++d) {
+        const uint32_t hi = order[d];
+        t.list_of(hi, &ids);
+        DevNode& dn = out->nodes[d];
+        dn.tri_first = (uint32_t)out->tris.size();
+        dn.tri_n = (uint32_t)ids.size();
+        out->n_stored += ids.size();
+        if (hi == 0) out->root_list = ids.size();
+        else out->max_list = std::max<uint64_t>(out->max_list, ids.size());
+        if (cull_threshold && ids.size() > cull_threshold) {
+            std::vector<double> boxes(6 * ids.size());
+            for (size_t i = 0; i < ids.size(); ++i) tri_box(v + 9 * (size_t)ids[i], &boxes[6 * i]);
+            CullBuilder cb{v, ids, std::move(boxes), out->cull, dn.tri_first};
+            dn.cull_root = cb.build(0, (uint32_t)ids.size());
+        }
+        for (uint32_t id : ids) {
+            const double* p = v + 9 * (size_t)id;
+            DevTri r{};
+            for (int k = 0; k < 3; ++k) {
+                r.v1[k] = p[k];
+                r.e1[k] = p[3 + k] - p[k];  // ray.rs:60
+                r.e2[k] = p[6 + k] - p[k];  // ray.rs:61
+            }
+            r.id = id;
+            out->tris.push_back(r);
+        }
+    }
+}
+
+}  // namespace rrt

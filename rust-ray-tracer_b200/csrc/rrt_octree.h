@@ -1,0 +1,90 @@
+// rrt_octree.h — host-side octree of the reference (src/collision/octree.rs) as flat arrays, and the
+// pointer-free device layout it is flattened into.  Product code (not the oracle).
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+
+namespace rrt {
+
+constexpr int kMaxOctreeDepth = 48;  // reference recursion is unbounded; deeper trees are refused (RRT_ERR_DEPTH)
+
+// One reference OctantNode (octree.rs:7-12) without heap vectors: children are the 8 consecutive nodes
+// starting at first_child (octree.rs:226-237); the triangle list is an intrusive singly linked list
+// threaded through HostOctree::next (each triangle lives in at most one list).
+struct HostNode {
+    double box[6];             // min.xyz, max.xyz  (aabb.rs:4-7)
+    uint32_t first_child = 0;  // 0 = leaf
+    uint32_t triangle_count = 0;  // octree.rs:11 (everything that passed through, not the list length)
+    uint32_t head = UINT32_MAX, tail = UINT32_MAX;  // own list in insertion order
+    uint32_t list_len = 0;
+    uint32_t depth = 0;
+};
+
+struct HostOctree {
+    std::vector<HostNode> nodes;
+    std::vector<uint32_t> next;  // per triangle: next triangle in the same node list
+    uint64_t n_tris = 0, n_dropped = 0;
+    uint32_t max_depth = 0;
+
+    // Sequential insertion, bit-identical to Octree::push_triangle for i = 0..n-1 (octree.rs:41-108).
+    // v = n x 9 doubles. Returns false (err set) if the tree exceeds kMaxOctreeDepth.
+    bool build(const double* v, uint64_t n, const double root_min[3], const double root_max[3], std::string* err);
+    void list_of(uint32_t node, std::vector<uint32_t>* out) const;
+};
+
+// ---------------------------------------------------------------- device layout
+
+// Node kept on the device (only nodes with triangle_count > 0; empty ones return None at ray.rs:112
+// and the child sort is stable, so dropping them cannot change a result).  96 bytes.
+struct alignas(16) DevNode {
+    uint32_t first_child;        // device index of the first kept child (kept children are consecutive)
+    uint32_t child_mask;         // bit k = reference child k (order octree.rs:216-225) is kept
+    uint32_t tri_first, tri_n;   // own triangle records [tri_first, tri_first + tri_n)
+    double px[3], py[3], pz[3];  // the 3 planes per axis shared by the 8 child boxes: min, min+half, max
+                                 // (octree.rs:136-210) — 9 distinct slab numerators instead of 48
+    uint32_t cull_root;          // root of this list's culling hierarchy (UINT32_MAX = scan linearly)
+    uint32_t _pad;
+};
+static_assert(sizeof(DevNode) == 96, "DevNode layout");
+
+// Intersection record, 80 bytes = 5 x 16-byte vector loads. e1/e2 are the reference's own
+// `v2 - v1`, `v3 - v1` (ray.rs:60-61) evaluated once on the host in f64: same operands, same bits.
+struct alignas(16) DevTri {
+    double v1[3], e1[3], e2[3];
+    uint32_t id;   // index in `f`-line order (what hit-id planes report; also the in-list tie order)
+    uint32_t _pad;
+};
+static_assert(sizeof(DevTri) == 80, "DevTri layout");
+
+// Shading record by ORIGINAL triangle id, 128 bytes, touched only on hits (entities.rs:78-84).
+struct alignas(16) DevShade {
+    double n1[3], n2[3], n3[3];
+    double t1[2], t2[2], t3[2];
+    int32_t material;
+    int32_t _pad;
+};
+static_assert(sizeof(DevShade) == 128, "DevShade layout");
+
+// Culling hierarchy over one long node list (binary BVH, both child boxes in the parent). Boxes are
+// padded outward; every candidate it yields is still decided by the exact f64 Moller-Trumbore test.
+struct alignas(16) DevCull {
+    double box[2][6];     // child 0 / child 1 : min.xyz max.xyz (padded)
+    uint32_t child[2];    // >= 0x80000000: leaf, low bits = first record; else index of DevCull
+    uint32_t count[2];    // leaf: number of records
+};
+static_assert(sizeof(DevCull) == 112, "DevCull layout");
+
+struct FlatScene {
+    std::vector<DevNode> nodes;
+    std::vector<DevTri> tris;
+    std::vector<DevCull> cull;
+    uint64_t n_stored = 0, root_list = 0, max_list = 0;
+    uint32_t max_depth = 0;
+};
+
+// Flatten: renumber kept nodes breadth-first (siblings consecutive), concatenate node lists.
+// cull_threshold: lists longer than this get a culling hierarchy (0 = never).
+void flatten(const HostOctree& t, const double* v, uint32_t cull_threshold, FlatScene* out);
+
+}  // namespace rrt
