@@ -223,6 +223,11 @@ const char* rrt_obj_material_name(const rrt_obj* o, uint32_t i);
 uint32_t rrt_obj_n_textures(const rrt_obj* o);
 const char* rrt_obj_texture_name(const rrt_obj* o, uint32_t i);
 
+/* ---- diagnostics ---- */
+/* Measures the FP64 vector throughput WITHOUT FMA (separate DMUL + DADD, as the -fmad=false kernels issue
+ * them): the roofline denominator of this path. sm_clock_mhz (may be NULL) = nominal max clock. */
+int rrt_microbench_fp64(int device, double* tflops_no_fma, double* sm_clock_mhz);
+
 /* ---- headless output (stands in for the minifb window, engine.rs:122-167) ---- */
 int rrt_write_ppm(const char* path, const uint32_t* fb_0rgb, int32_t width, int32_t height);
 

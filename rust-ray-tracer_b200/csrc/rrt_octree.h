@@ -7,7 +7,7 @@
 
 namespace rrt {
 
-constexpr int kMaxOctreeDepth = 48;  // reference recursion is unbounded; deeper trees are refused (RRT_ERR_DEPTH)
+constexpr int kMaxOctreeDepth = 64;  // reference recursion is unbounded; deeper trees are refused (RRT_ERR_DEPTH)
 
 // One reference OctantNode (octree.rs:7-12) without heap vectors: children are the 8 consecutive nodes
 // starting at first_child (octree.rs:226-237); the triangle list is an intrusive singly linked list

@@ -1,0 +1,72 @@
+"""Size-independent properties at BASELINE.json's full sizes (the oracle would take minutes there)."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def render(rrt, rt, W, H, hits=False):
+    sc = rrt.Scene(W, H)
+    fb = sc.draw_scene(rt, want_hit_ids=hits).copy()
+    return fb, sc.hit_ids
+
+
+def test_config2_culled_equals_linear_scan(rrt, scenes, monkeypatch):
+    # config[1]: model2 at 1920x1080. The culling hierarchies are a conservative filter in front of the
+    # exact f64 test, so the frame must be IDENTICAL with them switched off.
+    sd = scenes("model2")
+    rt = rrt.RayTracer(sd)
+    fb, hit = render(rrt, rt, 1920, 1080, hits=True)
+    fb2, _ = render(rrt, rt, 1920, 1080)
+    assert np.array_equal(fb, fb2)                                  # idempotent
+    assert (fb[0] == 0).all() and (hit[0] == -1).all() and (fb >> 24 == 0).all()
+    monkeypatch.setenv("RRT_CULL_THRESHOLD", "0")
+    rt0 = rrt.RayTracer(sd)
+    assert rt0.stats()["n_cull_nodes"] == 0 and rt.stats()["n_cull_nodes"] > 0
+    fb0, hit0 = render(rrt, rt0, 1920, 1080, hits=True)
+    assert np.array_equal(hit, hit0) and np.array_equal(fb, fb0)
+    rt.close(); rt0.close()
+
+
+def test_config4_sharded_equals_whole(rrt):
+    # config[3] geometry (1M-triangle sphere grid) at 3840x2160: rendering interleaved tile rows on
+    # 1/2/4/8 "ranks" (here sequentially on one GPU) and de-interleaving must give the whole frame.
+    import torch
+    from rrt_b200.synthetic import sphere_grid
+    from rrt_b200.sharding import ShardedRenderer
+    sd = sphere_grid()
+    assert sd.n_tris == 999_936
+    rt = rrt.RayTracer(sd)
+    W, H = 3840, 2160
+    whole, _ = render(rrt, rt, W, H)
+    assert (whole[0] == 0).all() and (whole[1:] != 0x00FFFFFF).mean() > 0.2
+    p = rt.params(W, H)
+    L = rrt.abi.lib()
+    for G in (2, 8):
+        rs = [ShardedRenderer(rt, W, H, r, G, tile_rows=8) for r in range(G)]
+        gathered = torch.zeros((G, rs[0].rpb, W), dtype=torch.int32, device="cuda:0")
+        for r in rs:
+            r.render(p)
+            gathered[r.rank].copy_(r.local)
+        frame = torch.zeros((H, W), dtype=torch.int32, device="cuda:0")
+        rrt.abi.check(L.rrt_deinterleave_device(0, gathered.data_ptr(), rs[0].rpb, W, H, 8, G, frame.data_ptr(), None))
+        torch.cuda.synchronize()
+        assert np.array_equal(frame.cpu().numpy().view(np.uint32), whole)
+    rt.close()
+
+
+def test_counters_match_oracle_ray_counts(rrt, scenes):
+    # the instrumented kernel counts the same rays the oracle traces (primary / shadow / reflection)
+    from oracle.oracle import OracleScene
+    sd = scenes("model2")
+    rt = rrt.RayTracer(sd)
+    p = rt.params(160, 90)
+    c = rrt.abi.Counters()
+    rrt.abi.check(rrt.abi.lib().rrt_render_counters(rt.handle, C.byref(p), None, C.byref(c)))
+    _, _, _, oc = OracleScene(sd).render(p, counters=True)
+    assert (c.rays_primary, c.rays_shadow, c.rays_reflect) == (oc["rays_primary"], oc["rays_shadow"], oc["rays_reflect"])
+    assert 0 < c.mt_tests < oc["n_a"]          # culling: fewer exact tests than the reference executes
+    rt.close()
