@@ -227,6 +227,9 @@ const char* rrt_obj_texture_name(const rrt_obj* o, uint32_t i);
 /* Measures the FP64 vector throughput WITHOUT FMA (separate DMUL + DADD, as the -fmad=false kernels issue
  * them): the roofline denominator of this path. sm_clock_mhz (may be NULL) = nominal max clock. */
 int rrt_microbench_fp64(int device, double* tflops_no_fma, double* sm_clock_mhz);
+/* Checks the kernels' FMA-based quotient (RN(a/d) from RN(1/d), rrt_trace.cuh) bit-for-bit against the
+ * hardware IEEE division on ~n_pairs pseudo-random operand pairs inside its range condition. */
+int rrt_selftest_division(int device, uint64_t n_pairs, uint64_t* mismatches);
 
 /* ---- headless output (stands in for the minifb window, engine.rs:122-167) ---- */
 int rrt_write_ppm(const char* path, const uint32_t* fb_0rgb, int32_t width, int32_t height);

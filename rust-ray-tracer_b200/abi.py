@@ -80,7 +80,7 @@ SYMBOLS = [
     "rrt_octree_build", "rrt_octree_destroy", "rrt_octree_node_count", "rrt_octree_node", "rrt_octree_node_list",
     "rrt_obj_load", "rrt_obj_destroy", "rrt_obj_n_tris", "rrt_obj_v", "rrt_obj_vt", "rrt_obj_vn",
     "rrt_obj_material_id", "rrt_obj_n_materials", "rrt_obj_materials", "rrt_obj_material_name",
-    "rrt_obj_n_textures", "rrt_obj_texture_name", "rrt_write_ppm", "rrt_microbench_fp64",
+    "rrt_obj_n_textures", "rrt_obj_texture_name", "rrt_write_ppm", "rrt_microbench_fp64", "rrt_selftest_division",
 ]
 
 _lib = None
@@ -139,6 +139,7 @@ def lib():
     L.rrt_obj_texture_name.restype = C.c_char_p
     L.rrt_write_ppm.argtypes = [C.c_char_p, vp, i32, i32]
     L.rrt_microbench_fp64.argtypes = [C.c_int, dp, dp]
+    L.rrt_selftest_division.argtypes = [C.c_int, u64, C.POINTER(u64)]
     _lib = L
     return L
 

@@ -156,7 +156,7 @@ int rrt_shard_rows(int32_t height, const rrt_shard* sh) {
 int rrt_scene_create(const rrt_scene_desc* d, int device, rrt_scene** out) {
     if (!d || !out) return fail(RRT_ERR_INVALID, "null argument");
     *out = nullptr;
-    if (d->n_tris > 0x7FFFFFF0ull) return fail(RRT_ERR_INVALID, "too many triangles");
+    if (d->n_tris >= (1ull << 28)) return fail(RRT_ERR_INVALID, "too many triangles (record index is 28 bits)");
     if (d->n_tris && (!d->v || !d->vt || !d->vn || !d->material_id)) return fail(RRT_ERR_INVALID, "null triangle arrays");
     // validation the reference performs by panicking (utils.rs:61 unwrap; Vec index out of range)
     for (uint32_t i = 0; i < d->n_textures; ++i)
@@ -208,6 +208,7 @@ int rrt_scene_create(const rrt_scene_desc* d, int device, rrt_scene** out) {
     if ((rc = sc->upload(flat.cull.data(), flat.cull.size(), &sc->dev.cull))) return rc;
     sc->dev.n_nodes = (uint32_t)flat.nodes.size();
     sc->dev.root_tri_count = st.n_tris_stored ? 1u : 0u;
+    sc->dev.planes_safe = (flat.planes_safe && !std::getenv("RRT_SLOW_DIV")) ? 1u : 0u;
 
     // shading records by original triangle id (entities.rs:78-84)
     {

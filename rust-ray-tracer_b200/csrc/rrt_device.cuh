@@ -33,6 +33,7 @@ struct DevScene {
     const DevTexture* tex;
     uint32_t n_nodes;
     uint32_t root_tri_count;   // nodes[0].triangle_count analogue: 0 => every ray misses (ray.rs:112-114)
+    uint32_t planes_safe;      // octree planes satisfy the range condition of the FMA quotient path
 };
 
 struct DevCounters {

@@ -136,7 +136,8 @@ struct CullBuilder {
     std::vector<double> boxes;        // per entry of ids (parallel array), 6 doubles
     std::vector<DevCull>& out;
     uint32_t rec_base;                // record index of ids[0]
-    static constexpr uint32_t kLeaf = 4;
+    bool tight;                       // false: infinite boxes (culling off, every record is tested)
+    uint32_t leaf_max;                // records per leaf (<= 8: 3-bit count field)
 
     static void pad_box(double* b) {
         for (int k = 0; k < 3; ++k) {
@@ -147,6 +148,10 @@ struct CullBuilder {
         }
     }
     void bounds(uint32_t lo, uint32_t hi, double* b) const {
+        if (!tight) {
+            for (int k = 0; k < 3; ++k) { b[k] = -INFINITY; b[3 + k] = INFINITY; }
+            return;
+        }
         for (int k = 0; k < 3; ++k) { b[k] = INFINITY; b[3 + k] = -INFINITY; }
         for (uint32_t i = lo; i < hi; ++i)
             for (int k = 0; k < 3; ++k) {
@@ -230,29 +235,23 @@ struct CullBuilder {
         if (i == lo || i == hi) return lo + (hi - lo) / 2;
         return i;
     }
-    // Builds the subtree over [lo,hi) (hi-lo > kLeaf) and returns its DevCull index.
-    uint32_t build(uint32_t lo, uint32_t hi) {
+    static uint32_t leaf_word(uint32_t first, uint32_t n) { return 0x80000000u | ((n - 1u) << 28) | first; }
+    // Builds the subtree over [lo,hi) (hi-lo > leaf_max) and returns its DevCull index. SAH splits can be
+    // arbitrarily unbalanced, so below depth 30 the split is by count: total depth <= 30 + 28 < kMaxCullDepth.
+    uint32_t build(uint32_t lo, uint32_t hi, int depth = 0) {
         const uint32_t me = (uint32_t)out.size();
         out.emplace_back();
-        const uint32_t mid = split(lo, hi);
+        const uint32_t mid = (tight && depth < 30) ? split(lo, hi) : lo + (hi - lo) / 2;
         const uint32_t r[3] = {lo, mid, hi};
         for (int s = 0; s < 2; ++s) {
             double b[6];
             bounds(r[s], r[s + 1], b);
             pad_box(b);
             const uint32_t n = r[s + 1] - r[s];
-            uint32_t child, count;
-            if (n <= kLeaf) {
-                child = 0x80000000u | (rec_base + r[s]);
-                count = n;
-            } else {
-                child = build(r[s], r[s + 1]);
-                count = 0;
-            }
+            const uint32_t child = (n <= leaf_max) ? leaf_word(rec_base + r[s], n) : build(r[s], r[s + 1], depth + 1);
             DevCull& c = out[me];  // re-fetch: vector may have grown
             std::memcpy(c.box[s], b, sizeof b);
             c.child[s] = child;
-            c.count[s] = count;
         }
         return me;
     }
@@ -265,6 +264,7 @@ void flatten(const HostOctree& t, const double* v, uint32_t cull_threshold, Flat
     out->tris.clear();
     out->cull.clear();
     out->n_stored = out->root_list = out->max_list = 0;
+    out->planes_safe = true;
     out->max_depth = t.max_depth;
     if (t.nodes.empty() || t.nodes[0].triangle_count == 0) {
         // ray.rs:112-114: an empty root returns None for every ray; keep one inert node.
@@ -297,6 +297,15 @@ void flatten(const HostOctree& t, const double* v, uint32_t cull_threshold, Flat
         }
         out->nodes[d] = dn;
     }
+    // range condition of the FMA quotient path (rrt_trace.cuh): every plane is 0 or in [2^-400, 2^401)
+    out->planes_safe = true;
+    for (const DevNode& dn : out->nodes)
+        if (dn.child_mask)
+            for (int k = 0; k < 9; ++k) {
+                const double p = k < 3 ? dn.px[k] : (k < 6 ? dn.py[k - 3] : dn.pz[k - 6]);
+                const double a = std::fabs(p);
+                if (!(p == 0.0 || (a >= std::ldexp(1.0, -400) && a < std::ldexp(1.0, 401)))) out->planes_safe = false;
+            }
     // triangle records, node by node
     std::vector<uint32_t> ids;
     for (size_t d = 0; d < order.size(); ++d) {
@@ -308,10 +317,15 @@ void flatten(const HostOctree& t, const double* v, uint32_t cull_threshold, Flat
         out->n_stored += ids.size();
         if (hi == 0) out->root_list = ids.size();
         else out->max_list = std::max<uint64_t>(out->max_list, ids.size());
-        if (cull_threshold && ids.size() > cull_threshold) {
+        if (ids.empty()) {
+            dn.cull_root = UINT32_MAX;
+        } else if (ids.size() <= 8) {
+            dn.cull_root = CullBuilder::leaf_word(dn.tri_first, (uint32_t)ids.size());  // short list: one leaf
+        } else {
+            const bool tight = cull_threshold != 0;
             std::vector<double> boxes(6 * ids.size());
             for (size_t i = 0; i < ids.size(); ++i) tri_box(v + 9 * (size_t)ids[i], &boxes[6 * i]);
-            CullBuilder cb{v, ids, std::move(boxes), out->cull, dn.tri_first};
+            CullBuilder cb{v, ids, std::move(boxes), out->cull, dn.tri_first, tight, tight ? 4u : 8u};
             dn.cull_root = cb.build(0, (uint32_t)ids.size());
         }
         for (uint32_t id : ids) {

@@ -7,7 +7,8 @@
 
 namespace rrt {
 
-constexpr int kMaxOctreeDepth = 64;  // reference recursion is unbounded; deeper trees are refused (RRT_ERR_DEPTH)
+constexpr int kMaxOctreeDepth = 64;
+constexpr int kMaxCullDepth = 62;     // depth bound of a per-list culling hierarchy (builder enforces it)  // reference recursion is unbounded; deeper trees are refused (RRT_ERR_DEPTH)
 
 // One reference OctantNode (octree.rs:7-12) without heap vectors: children are the 8 consecutive nodes
 // starting at first_child (octree.rs:226-237); the triangle list is an intrusive singly linked list
@@ -43,7 +44,8 @@ struct alignas(16) DevNode {
     uint32_t tri_first, tri_n;   // own triangle records [tri_first, tri_first + tri_n)
     double px[3], py[3], pz[3];  // the 3 planes per axis shared by the 8 child boxes: min, min+half, max
                                  // (octree.rs:136-210) — 9 distinct slab numerators instead of 48
-    uint32_t cull_root;          // root of this list's culling hierarchy (UINT32_MAX = scan linearly)
+    uint32_t cull_root;          // entry of this list's culling hierarchy: a DevCull index, or a leaf word
+                                 // (bit31 | (count-1) << 28 | first record) when the list has <= 8 records
     uint32_t _pad;
 };
 static_assert(sizeof(DevNode) == 96, "DevNode layout");
@@ -70,8 +72,8 @@ static_assert(sizeof(DevShade) == 128, "DevShade layout");
 // padded outward; every candidate it yields is still decided by the exact f64 Moller-Trumbore test.
 struct alignas(16) DevCull {
     double box[2][6];     // child 0 / child 1 : min.xyz max.xyz (padded)
-    uint32_t child[2];    // >= 0x80000000: leaf, low bits = first record; else index of DevCull
-    uint32_t count[2];    // leaf: number of records
+    uint32_t child[2];    // bit31 set: leaf = bit31 | (count-1) << 28 | first record; else index of DevCull
+    uint32_t _pad[2];
 };
 static_assert(sizeof(DevCull) == 112, "DevCull layout");
 
@@ -81,10 +83,13 @@ struct FlatScene {
     std::vector<DevCull> cull;
     uint64_t n_stored = 0, root_list = 0, max_list = 0;
     uint32_t max_depth = 0;
+    bool planes_safe = true;   // every octree plane is 0 or has magnitude in [2^-400, 2^401) (rrt_trace.cuh)
 };
 
 // Flatten: renumber kept nodes breadth-first (siblings consecutive), concatenate node lists.
-// cull_threshold: lists longer than this get a culling hierarchy (0 = never).
+// cull_threshold: lists longer than this get a culling hierarchy with tight (padded) boxes.
+// 0 = culling off: long lists still go through the same hierarchy code, but with infinite boxes, so
+// every record of the list is tested (the exact linear scan of the reference, in another order).
 void flatten(const HostOctree& t, const double* v, uint32_t cull_threshold, FlatScene* out);
 
 }  // namespace rrt

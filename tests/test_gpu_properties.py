@@ -25,7 +25,13 @@ def test_config2_culled_equals_linear_scan(rrt, scenes, monkeypatch):
     assert (fb[0] == 0).all() and (hit[0] == -1).all() and (fb >> 24 == 0).all()
     monkeypatch.setenv("RRT_CULL_THRESHOLD", "0")
     rt0 = rrt.RayTracer(sd)
-    assert rt0.stats()["n_cull_nodes"] == 0 and rt.stats()["n_cull_nodes"] > 0
+    # culling off = the same hierarchy code with infinite boxes: every record of a visited list is tested
+    def mt_tests(r):
+        c = rrt.abi.Counters()
+        p = r.params(480, 270)
+        rrt.abi.check(rrt.abi.lib().rrt_render_counters(r.handle, C.byref(p), None, C.byref(c)))
+        return c.mt_tests
+    assert mt_tests(rt0) > 20 * mt_tests(rt)
     fb0, hit0 = render(rrt, rt0, 1920, 1080, hits=True)
     assert np.array_equal(hit, hit0) and np.array_equal(fb, fb0)
     rt.close(); rt0.close()
@@ -70,3 +76,23 @@ def test_counters_match_oracle_ray_counts(rrt, scenes):
     assert (c.rays_primary, c.rays_shadow, c.rays_reflect) == (oc["rays_primary"], oc["rays_shadow"], oc["rays_reflect"])
     assert 0 < c.mt_tests < oc["n_a"]          # culling: fewer exact tests than the reference executes
     rt.close()
+
+
+def test_fma_quotient_equals_ieee_division(rrt):
+    # the child-slab quotients use RN(1/d) + two FMA corrections instead of nine divisions per node;
+    # every such quotient must be the IEEE quotient, bit for bit (2^31 operand pairs, hard mantissas included)
+    n = C.c_uint64(0)
+    rrt.abi.check(rrt.abi.lib().rrt_selftest_division(0, 1 << 31, C.byref(n)))
+    assert n.value == 0
+
+
+def test_fma_quotient_path_equals_division_path(rrt, scenes, monkeypatch):
+    # same frame with the FMA quotient path disabled (true divisions everywhere): identical output
+    sd = scenes("model2")
+    rt = rrt.RayTracer(sd)
+    fb, hit = render(rrt, rt, 960, 540, hits=True)
+    monkeypatch.setenv("RRT_SLOW_DIV", "1")
+    rt2 = rrt.RayTracer(sd)
+    fb2, hit2 = render(rrt, rt2, 960, 540, hits=True)
+    assert np.array_equal(fb, fb2) and np.array_equal(hit, hit2)
+    rt.close(); rt2.close()
