@@ -49,7 +49,8 @@ struct rrt_scene {
     // scratch for the host-buffer entry points, grown on demand
     uint32_t* d_fb = nullptr;
     int32_t* d_hit = nullptr;
-    size_t fb_cap = 0, hit_cap = 0;
+    uint32_t* d_scratch = nullptr;   // per-pixel accumulators + sample-queue head of the persistent kernel
+    size_t fb_cap = 0, hit_cap = 0, scratch_cap = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
 
     template <class T>
@@ -68,6 +69,7 @@ struct rrt_scene {
         for (void* p : allocs) cudaFree(p);
         if (d_fb) cudaFree(d_fb);
         if (d_hit) cudaFree(d_hit);
+        if (d_scratch) cudaFree(d_scratch);
         if (ev0) cudaEventDestroy(ev0);
         if (ev1) cudaEventDestroy(ev1);
     }
@@ -296,7 +298,8 @@ int rrt_render_device(rrt_scene* s, const rrt_render_params* p, const rrt_shard*
     int rc = make_params(p, shard, &P);
     if (rc) return rc;
     CU(cudaSetDevice(s->device));
-    CU(launch_render(s->dev, P, d_fb, d_hit_ids, nullptr, (cudaStream_t)cuda_stream));
+    if ((rc = ensure(&s->d_scratch, &s->scratch_cap, render_scratch_words(P.n_rows_local, P.W)))) return rc;
+    CU(launch_render(s->dev, P, d_fb, d_hit_ids, s->d_scratch, nullptr, (cudaStream_t)cuda_stream));
     return RRT_OK;
 }
 
@@ -309,8 +312,9 @@ int rrt_render(rrt_scene* s, const rrt_render_params* p, uint32_t* fb, int32_t* 
     const size_t n = (size_t)P.W * P.H;
     if ((rc = ensure(&s->d_fb, &s->fb_cap, n))) return rc;
     if (hit_ids && (rc = ensure(&s->d_hit, &s->hit_cap, n * 4))) return rc;
+    if ((rc = ensure(&s->d_scratch, &s->scratch_cap, render_scratch_words(P.n_rows_local, P.W)))) return rc;
     CU(cudaEventRecord(s->ev0, 0));
-    CU(launch_render(s->dev, P, s->d_fb, hit_ids ? s->d_hit : nullptr, nullptr, 0));
+    CU(launch_render(s->dev, P, s->d_fb, hit_ids ? s->d_hit : nullptr, s->d_scratch, nullptr, 0));
     CU(cudaEventRecord(s->ev1, 0));
     CU(cudaMemcpy(fb, s->d_fb, n * sizeof(uint32_t), cudaMemcpyDeviceToHost));
     if (hit_ids) CU(cudaMemcpy(hit_ids, s->d_hit, n * 4 * sizeof(int32_t), cudaMemcpyDeviceToHost));
@@ -329,7 +333,8 @@ int rrt_render_counters(rrt_scene* s, const rrt_render_params* p, uint32_t* fb, 
     DevBuf c;
     if ((rc = c.alloc(sizeof(DevCounters)))) return rc;
     CU(cudaMemset(c.p, 0, sizeof(DevCounters)));
-    CU(launch_render(s->dev, P, s->d_fb, nullptr, (DevCounters*)c.p, 0));
+    if ((rc = ensure(&s->d_scratch, &s->scratch_cap, render_scratch_words(P.n_rows_local, P.W)))) return rc;
+    CU(launch_render(s->dev, P, s->d_fb, nullptr, s->d_scratch, (DevCounters*)c.p, 0));
     DevCounters h;
     CU(cudaMemcpy(&h, c.p, sizeof h, cudaMemcpyDeviceToHost));
     if (fb) CU(cudaMemcpy(fb, s->d_fb, n * sizeof(uint32_t), cudaMemcpyDeviceToHost));

@@ -7,9 +7,15 @@ namespace rrt {
 
 namespace {
 
-constexpr int kBlock = 256;      // 8 warps
-constexpr int kTileW = 16;       // pixels per block tile: 4 warps across x 4 px
-constexpr int kTileH = 4;        //                        2 warps down   x 2 px
+#ifndef RRT_BLOCK
+#define RRT_BLOCK 128
+#endif
+#ifndef RRT_MIN_BLOCKS
+#define RRT_MIN_BLOCKS 4
+#endif
+constexpr int kBlock = RRT_BLOCK;
+constexpr int kTileW = 16;       // samples are enumerated in 16x4-pixel blocks of eight 4x2-pixel tiles,
+constexpr int kTileH = 4;        // 4 supersamples per pixel: 32 consecutive indices = one 8x4 half-pixel lattice
 
 // compact row k of this shard -> buffer row (rrt_shard in rrt.h)
 __device__ __forceinline__ int buffer_row(const DevParams& P, int k) {
@@ -18,50 +24,101 @@ __device__ __forceinline__ int buffer_row(const DevParams& P, int k) {
     return (P.shard_index + jl * P.n_shards) * P.tile_rows + within;
 }
 
-// One thread per supersample: a warp covers 4x2 pixels x 4 samples (an 8x4 lattice of half-pixel
-// steps), lanes 4p..4p+3 are the samples d1..d4 of pixel p (engine.rs:207-236).
+// Persistent render kernel (Scene::draw_scene, engine.rs:186-255).  One lane = one supersample at a time.
+// Whenever lanes of a warp run dry — their ray missed, or finished its shadow / mirror chain early — they
+// fetch the next sample indices from a global queue (one atomicAdd per warp per refill) instead of idling
+// until the slowest lane of the warp is done.  All lanes meet in the single traverse() call site whatever
+// kind of ray (primary, shadow, reflection) they carry.
+// The 4 samples of a pixel (engine.rs:207-236) may be finished by different lanes at different times:
+// each adds its colour into a packed per-pixel accumulator (10 bits per channel + 2-bit arrival count);
+// the 4th arrival divides by 4 (Color::mix, entities.rs:49-69) and stores the pixel (entities.rs:32-36).
 template <bool COUNT>
-__global__ void __launch_bounds__(kBlock)
+__global__ void __launch_bounds__(kBlock, RRT_MIN_BLOCKS)
 render_kernel(const DevScene sc, const __grid_constant__ DevParams P, uint32_t* __restrict__ fb,
-              int32_t* __restrict__ hit_ids, DevCounters* __restrict__ counters, const int tiles_x) {
-    const int tile = blockIdx.x;
-    const int by = tile / tiles_x, bx = tile - by * tiles_x;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int p = lane >> 2, k = lane & 3;
-    const int col = bx * kTileW + (warp & 3) * 4 + (p & 3);
-    const int krow = by * kTileH + (warp >> 2) * 2 + (p >> 2);
-    const bool in_buf = col < P.W && krow < P.n_rows_local;
-    const int r = buffer_row(P, krow);
-    // put_pixel: new_x = x + W/2, new_y = H - (y + H/2)  (engine.rs:147-150)
-    const int x = col - P.W / 2;
-    const int y = P.H - r - P.H / 2;
-    const bool traced = in_buf && r >= 1 && r < P.H && col < 2 * (P.W / 2) && y >= -(P.H / 2) && y < P.H / 2;
+              int32_t* __restrict__ hit_ids, uint32_t* __restrict__ acc, unsigned long long* __restrict__ next,
+              DevCounters* __restrict__ counters, const int tiles_x, const unsigned long long total) {
+    const unsigned lane = threadIdx.x & 31u;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    RayState st;
+    bool active = false, drained = false;
+    size_t pix = 0;
+    unsigned k = 0;
+    TraceCount tc_total;
+    uint32_t n_primary = 0, n_shadow = 0, n_reflect = 0;
 
-    uint32_t rgb = 0;
-    int32_t hid = -1;
-    RayCount rc;
-    if (traced) {
-        const double fx = (k & 1) ? ((double)x + 0.5) : (double)x;   // engine.rs:208,218
-        const double fy = (k & 2) ? ((double)y + 0.5) : (double)y;   // engine.rs:209,226
-        V3 d{fx * P.xs, fy * P.ys, P.zv};
-        if (P.use_rot) {  // extension (rrt.h): d' = R d
-            d = V3{(P.rot[0] * d.x + P.rot[1] * d.y) + P.rot[2] * d.z,
-                   (P.rot[3] * d.x + P.rot[4] * d.y) + P.rot[5] * d.z,
-                   (P.rot[6] * d.x + P.rot[7] * d.y) + P.rot[8] * d.z};
+    for (;;) {
+        // ---- refill idle lanes from the global sample queue
+        const unsigned idle = __ballot_sync(0xFFFFFFFFu, !active);
+        if (idle && !drained) {
+            const int leader = __ffs(idle) - 1;
+            unsigned long long base = 0;
+            if ((int)lane == leader) base = atomicAdd(next, (unsigned long long)__popc(idle));
+            base = __shfl_sync(0xFFFFFFFFu, base, leader);
+            if (base + __popc(idle) >= total) drained = true;  // warp-uniform: the queue is (about to be) empty
+            if (!active) {
+                const unsigned long long s = base + __popc(idle & lt_mask);
+                if (s < total) {
+                    const unsigned long long tile = s >> 5;
+                    const unsigned l = (unsigned)s & 31u, p = l >> 2;
+                    const unsigned long long blk = tile >> 3;
+                    const unsigned w = (unsigned)tile & 7u;
+                    const int by = (int)(blk / (unsigned)tiles_x), bx = (int)(blk - (unsigned long long)by * tiles_x);
+                    const int col = bx * kTileW + (int)(w & 3u) * 4 + (int)(p & 3u);
+                    const int krow = by * kTileH + (int)(w >> 2) * 2 + (int)(p >> 2);
+                    k = l & 3u;
+                    if (col < P.W && krow < P.n_rows_local) {
+                        pix = (size_t)krow * P.W + col;
+                        const int r = buffer_row(P, krow);
+                        // put_pixel: new_x = x + W/2, new_y = H - (y + H/2)  (engine.rs:147-150)
+                        const int x = col - P.W / 2;
+                        const int y = P.H - r - P.H / 2;
+                        const bool traced = r >= 1 && r < P.H && col < 2 * (P.W / 2) && y >= -(P.H / 2) && y < P.H / 2;
+                        if (traced) {
+                            const double fx = (k & 1u) ? ((double)x + 0.5) : (double)x;   // engine.rs:208,218
+                            const double fy = (k & 2u) ? ((double)y + 0.5) : (double)y;   // engine.rs:209,226
+                            V3 d{fx * P.xs, fy * P.ys, P.zv};
+                            if (P.use_rot) {  // extension (rrt.h): d' = R d
+                                d = V3{(P.rot[0] * d.x + P.rot[1] * d.y) + P.rot[2] * d.z,
+                                       (P.rot[3] * d.x + P.rot[4] * d.y) + P.rot[5] * d.z,
+                                       (P.rot[6] * d.x + P.rot[7] * d.y) + P.rot[8] * d.z};
+                            }
+                            st.begin(V3{P.ox, P.oy, P.oz}, d);
+                            active = true;
+                            if (COUNT) n_primary++;
+                        } else {
+                            // never written by the reference (row 0, odd last column / row): stays 0, hit id -1
+                            if (hit_ids) hit_ids[pix * 4 + k] = -1;
+                            if ((atomicAdd(acc + pix, 1u << 30) >> 30) == 3u) fb[pix] = 0u;
+                        }
+                    }
+                }
+            }
         }
-        rgb = ray_colour<COUNT>(sc, P, V3{P.ox, P.oy, P.oz}, d, &hid, rc);
-    }
-    // Color::mix (entities.rs:49-69): per-channel integer mean of the 4 samples, truncating
-    uint32_t cr = rgb & 255u, cg = (rgb >> 8) & 255u, cb = (rgb >> 16) & 255u;
-    cr += __shfl_xor_sync(0xFFFFFFFFu, cr, 1); cg += __shfl_xor_sync(0xFFFFFFFFu, cg, 1); cb += __shfl_xor_sync(0xFFFFFFFFu, cb, 1);
-    cr += __shfl_xor_sync(0xFFFFFFFFu, cr, 2); cg += __shfl_xor_sync(0xFFFFFFFFu, cg, 2); cb += __shfl_xor_sync(0xFFFFFFFFu, cb, 2);
-    if (in_buf) {
-        const size_t pix = (size_t)krow * P.W + col;
-        if (k == 0) fb[pix] = traced ? ((cb >> 2) + ((cg >> 2) << 8) + ((cr >> 2) << 16)) : 0u;  // entities.rs:32-36
-        if (hit_ids) hit_ids[pix * 4 + k] = hid;
+        if (!__any_sync(0xFFFFFFFFu, active)) {
+            if (drained) break;
+            continue;
+        }
+        // ---- one traversal for every lane that carries a ray, whatever its kind
+        if (active) {
+            Hit h;
+            traverse<COUNT>(sc, st.so, st.sd, st.smax, st.shadow, h, tc_total);
+            if (st.advance<COUNT>(sc, P, h)) {
+                active = false;
+                if (hit_ids) hit_ids[pix * 4 + k] = st.hit0;
+                const uint32_t c = st.res;
+                const uint32_t add = (c & 255u) | (((c >> 8) & 255u) << 10) | (((c >> 16) & 255u) << 20) | (1u << 30);
+                const uint32_t old = atomicAdd(acc + pix, add);
+                if ((old >> 30) == 3u) {  // 4th sample of this pixel: Color::mix + pack (entities.rs:32-36,49-69)
+                    const uint32_t sum = old + add;
+                    const uint32_t r = (sum & 1023u) >> 2, g = ((sum >> 10) & 1023u) >> 2, b = ((sum >> 20) & 1023u) >> 2;
+                    fb[pix] = b + (g << 8) + (r << 16);
+                }
+            }
+        }
     }
     if (COUNT) {
-        unsigned long long v[7] = {rc.primary, rc.shadow, rc.reflect, rc.tc.mt, rc.tc.box, rc.tc.cull, rc.tc.nodes};
+        n_shadow = st.rc.shadow; n_reflect = st.rc.reflect;
+        unsigned long long v[7] = {n_primary, n_shadow, n_reflect, tc_total.mt, tc_total.box, tc_total.cull, tc_total.nodes};
 #pragma unroll
         for (int i = 0; i < 7; ++i) {
             for (int o = 16; o > 0; o >>= 1) v[i] += __shfl_xor_sync(0xFFFFFFFFu, v[i], o);
@@ -92,10 +149,14 @@ colour_kernel(const DevScene sc, const __grid_constant__ DevParams P, const uint
               const double* __restrict__ d, uint8_t* __restrict__ out_rgb) {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    int32_t hid;
-    RayCount rc;
-    const uint32_t c = ray_colour<false>(sc, P, V3{o[3 * i], o[3 * i + 1], o[3 * i + 2]},
-                                         V3{d[3 * i], d[3 * i + 1], d[3 * i + 2]}, &hid, rc);
+    RayState st;
+    TraceCount tc;
+    st.begin(V3{o[3 * i], o[3 * i + 1], o[3 * i + 2]}, V3{d[3 * i], d[3 * i + 1], d[3 * i + 2]});
+    Hit h;
+    do {
+        traverse<false>(sc, st.so, st.sd, st.smax, st.shadow, h, tc);
+    } while (!st.advance<false>(sc, P, h));
+    const uint32_t c = st.res;
     out_rgb[3 * i] = (uint8_t)(c & 255u); out_rgb[3 * i + 1] = (uint8_t)((c >> 8) & 255u); out_rgb[3 * i + 2] = (uint8_t)((c >> 16) & 255u);
 }
 
@@ -112,17 +173,41 @@ __global__ void deinterleave_kernel(const uint32_t* __restrict__ g, int rows_per
 
 }  // namespace
 
-cudaError_t launch_render(const DevScene& sc, const DevParams& P, uint32_t* d_fb, int32_t* d_hit,
+// scratch = (n_rows_local*W + 2) u32 words: per-pixel accumulators followed by the 64-bit queue head.
+cudaError_t launch_render(const DevScene& sc, const DevParams& P, uint32_t* d_fb, int32_t* d_hit, uint32_t* d_scratch,
                           DevCounters* d_counters, cudaStream_t stream) {
     const int tiles_x = (P.W + kTileW - 1) / kTileW, tiles_y = (P.n_rows_local + kTileH - 1) / kTileH;
-    const long long tiles = (long long)tiles_x * tiles_y;
-    if (tiles <= 0) return cudaSuccess;
+    const unsigned long long total = (unsigned long long)tiles_x * tiles_y * (kTileW * kTileH * 4);
+    if (total == 0) return cudaSuccess;
+    const size_t npix = (size_t)P.n_rows_local * P.W;
+    const size_t head = (npix + 1) & ~(size_t)1;  // 8-byte aligned
+    cudaError_t e = cudaMemsetAsync(d_scratch, 0, (head + 2) * sizeof(uint32_t), stream);
+    if (e != cudaSuccess) return e;
+    static int blocks_per_sm[2] = {0, 0};
+    static int n_sm = 0;
+    const int which = d_counters ? 1 : 0;
+    if (!blocks_per_sm[which]) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
+        int b = 0;
+        e = d_counters ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, render_kernel<true>, kBlock, 0)
+                       : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, render_kernel<false>, kBlock, 0);
+        if (e != cudaSuccess) return e;
+        blocks_per_sm[which] = b > 0 ? b : 1;
+    }
+    unsigned long long want = (total + kBlock - 1) / kBlock;
+    const unsigned long long resident = (unsigned long long)n_sm * blocks_per_sm[which];
+    const unsigned grid = (unsigned)(want < resident ? want : resident);  // persistent: one wave
+    unsigned long long* next = reinterpret_cast<unsigned long long*>(d_scratch + head);
     if (d_counters)
-        render_kernel<true><<<(unsigned)tiles, kBlock, 0, stream>>>(sc, P, d_fb, d_hit, d_counters, tiles_x);
+        render_kernel<true><<<grid, kBlock, 0, stream>>>(sc, P, d_fb, d_hit, d_scratch, next, d_counters, tiles_x, total);
     else
-        render_kernel<false><<<(unsigned)tiles, kBlock, 0, stream>>>(sc, P, d_fb, d_hit, nullptr, tiles_x);
+        render_kernel<false><<<grid, kBlock, 0, stream>>>(sc, P, d_fb, d_hit, d_scratch, next, nullptr, tiles_x, total);
     return cudaGetLastError();
 }
+
+size_t render_scratch_words(int n_rows_local, int W) { return (((size_t)n_rows_local * W + 1) & ~(size_t)1) + 2; }
 
 cudaError_t launch_trace(const DevScene& sc, uint64_t n, const double* o, const double* d, const double* max_t,
                          int32_t* out_tri, double* out_tuv, cudaStream_t stream) {

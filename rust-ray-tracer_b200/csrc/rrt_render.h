@@ -8,8 +8,10 @@ namespace rrt {
 
 struct DevParams;
 
-cudaError_t launch_render(const DevScene& sc, const DevParams& P, uint32_t* d_fb, int32_t* d_hit,
+// d_scratch: render_scratch_words(P.n_rows_local, P.W) u32 words of device memory (zeroed by the launcher)
+cudaError_t launch_render(const DevScene& sc, const DevParams& P, uint32_t* d_fb, int32_t* d_hit, uint32_t* d_scratch,
                           DevCounters* d_counters, cudaStream_t stream);
+size_t render_scratch_words(int n_rows_local, int W);
 cudaError_t launch_trace(const DevScene& sc, uint64_t n, const double* o, const double* d, const double* max_t,
                          int32_t* out_tri, double* out_tuv, cudaStream_t stream);
 cudaError_t launch_colours(const DevScene& sc, const DevParams& P, uint64_t n, const double* o, const double* d,

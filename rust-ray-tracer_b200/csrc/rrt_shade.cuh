@@ -48,35 +48,55 @@ __device__ __forceinline__ void add_light(V3& I, const DevMaterial* __restrict__
     if (!spec) I = I + V3{0.0, 0.0, 0.0};
 }
 
-// Returns the colour packed r | g<<8 | b<<16; *hit0 = depth-0 triangle id or -1.
-template <bool COUNT>
-__device__ __forceinline__ uint32_t ray_colour(const DevScene& sc, const DevParams& P, V3 ro, V3 rd, int32_t* hit0,
-                                               RayCount& rc) {
-    const double kInf = __longlong_as_double(0x7FF0000000000000ll);
+// Per-ray state of RayTracer::get_ray_colour_recursive (raytracer.rs:33-112) between traversals.
+// Usage:  st.begin(o, d);  do { traverse(st.so, st.sd, st.smax, st.shadow, h); } while (!st.advance(sc, P, h));
+// then st.res is the colour packed r | g<<8 | b<<16 and st.hit0 the depth-0 triangle id (-1 = miss).
+struct RayState {
     // reflection stack: local colour and reflectivity of every open level (raytracer.rs:89-101)
     double lx[kMaxReflectDepth], ly[kMaxReflectDepth], lz[kMaxReflectDepth], lk[kMaxReflectDepth];
-    int depth = 0;
-    uint32_t res = 0x00FFFFFFu;
+    V3 ro, rd;            // current primary / reflection ray
+    V3 pt, n, I;          // hit point, shading normal, accumulated light (survive shadow traversals)
+    V3 so, sd;            // the ray to hand to traverse()
+    double smax;
+    const DevMaterial* mat;
+    uint32_t texel, res;
+    int32_t hit0;
+    int depth, li;
+    bool shadow;
+    RayCount rc;
 
-    // state that survives shadow traversals
-    V3 pt{0, 0, 0}, n{0, 0, 0}, I{0, 0, 0};
-    V3 so = ro, sd = rd;        // the ray handed to traverse()
-    double smax = kInf;
-    bool shadow = false;
-    uint32_t texel = 0;
-    const DevMaterial* mat = nullptr;
-    int li = 0;
-    if (COUNT) rc.primary++;
+    __device__ __forceinline__ void begin(const V3& o, const V3& d) {
+        ro = o; rd = d; so = o; sd = d;
+        smax = __longlong_as_double(0x7FF0000000000000ll);
+        shadow = false;
+        depth = 0; li = 0;
+        res = 0x00FFFFFFu;
+        hit0 = -1;
+        mat = nullptr;
+        texel = 0;
+        pt = n = I = V3{0.0, 0.0, 0.0};
+    }
 
-    for (;;) {
-        Hit h;
-        traverse<COUNT>(sc, so, sd, smax, shadow, h, rc.tc);
+    // unwind the open mirror levels: every level re-quantises to u8 (raytracer.rs:89-101)
+    __device__ __forceinline__ void unwind() {
+        while (depth > 0) {
+            --depth;
+            const double k = lk[depth];
+            const V3 rv{(double)(res & 255u), (double)((res >> 8) & 255u), (double)((res >> 16) & 255u)};
+            const V3 fin = V3{lx[depth], ly[depth], lz[depth]} * (1.0 - k) + rv * k;  // raytracer.rs:95
+            res = rust_clamp_u8(fin.x) | (rust_clamp_u8(fin.y) << 8) | (rust_clamp_u8(fin.z) << 16);
+        }
+    }
 
+    // Consumes the result of the traversal just made; returns true when the colour is final.
+    template <bool COUNT>
+    __device__ __forceinline__ bool advance(const DevScene& sc, const DevParams& P, const Hit& h) {
         if (!shadow) {
-            if (depth == 0) *hit0 = (h.id == kNone) ? -1 : (int32_t)h.id;
+            if (depth == 0) hit0 = (h.id == kNone) ? -1 : (int32_t)h.id;
             if (h.id == kNone) {  // WHITE raytracer.rs:109-111
                 res = 0x00FFFFFFu;
-                break;
+                unwind();
+                return true;
             }
             // ---- hit set-up (raytracer.rs:38-57)
             const double2* sp2 = reinterpret_cast<const double2*>(sc.shade + h.id);
@@ -143,10 +163,9 @@ __device__ __forceinline__ uint32_t ray_colour(const DevScene& sc, const DevPara
                 smax = length(sd);                          // raytracer.rs:179
                 shadow = true;
                 if (COUNT) rc.shadow++;
-                break;
+                return false;
             }
         }
-        if (shadow) continue;
 
         // ---- local colour and optional mirror bounce (raytracer.rs:66-108)
         const V3 local{(double)(texel & 255u) * I.x, (double)((texel >> 8) & 255u) * I.y,
@@ -159,22 +178,15 @@ __device__ __forceinline__ uint32_t ray_colour(const DevScene& sc, const DevPara
             rd = ndir;
             lx[depth] = local.x; ly[depth] = local.y; lz[depth] = local.z; lk[depth] = kr;
             depth++;
-            so = ro; sd = rd; smax = kInf;
+            so = ro; sd = rd;
+            smax = __longlong_as_double(0x7FF0000000000000ll);
             if (COUNT) rc.reflect++;
-            continue;
+            return false;
         }
         res = rust_clamp_u8(local.x) | (rust_clamp_u8(local.y) << 8) | (rust_clamp_u8(local.z) << 16);  // raytracer.rs:104-108
-        break;
+        unwind();
+        return true;
     }
-    // unwind the open mirror levels: every level re-quantises to u8 (raytracer.rs:89-101)
-    while (depth > 0) {
-        --depth;
-        const double k = lk[depth];
-        const V3 rv{(double)(res & 255u), (double)((res >> 8) & 255u), (double)((res >> 16) & 255u)};
-        const V3 fin = V3{lx[depth], ly[depth], lz[depth]} * (1.0 - k) + rv * k;  // raytracer.rs:95
-        res = rust_clamp_u8(fin.x) | (rust_clamp_u8(fin.y) << 8) | (rust_clamp_u8(fin.z) << 16);
-    }
-    return res;
-}
+};
 
 }  // namespace rrt
