@@ -41,7 +41,7 @@ def up_to_date():
 def build(force=False, verbose=False):
     if not force and up_to_date():
         return OUT
-    cmd = [nvcc_path(), "-shared"] + NVCC_FLAGS
+    cmd = [nvcc_path(), "-shared"] + NVCC_FLAGS + os.environ.get("RRT_EXTRA_FLAGS", "").split()
     if os.path.exists("/usr/bin/g++"):
         cmd += ["-ccbin", "/usr/bin/g++"]
     cmd += [os.path.join(CSRC, s) for s in SOURCES] + ["-o", OUT]

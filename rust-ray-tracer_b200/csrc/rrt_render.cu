@@ -11,7 +11,7 @@ namespace {
 #define RRT_BLOCK 128
 #endif
 #ifndef RRT_MIN_BLOCKS
-#define RRT_MIN_BLOCKS 4
+#define RRT_MIN_BLOCKS 8
 #endif
 constexpr int kBlock = RRT_BLOCK;
 constexpr int kTileW = 16;       // samples are enumerated in 16x4-pixel blocks of eight 4x2-pixel tiles,
