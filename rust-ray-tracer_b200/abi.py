@@ -10,7 +10,8 @@ RRT_MAX_LIGHTS = 16
 LIGHT_AMBIENT, LIGHT_POINT, LIGHT_DIRECTIONAL = 0, 1, 2
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "librrt_b200.so")
+# RRT_LIB_PATH: development override (tools/variant_sweep.py times differently-built copies of the library)
+LIB_PATH = os.environ.get("RRT_LIB_PATH") or os.path.join(_HERE, "csrc", "librrt_b200.so")
 
 
 class RrtError(RuntimeError):

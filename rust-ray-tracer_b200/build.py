@@ -10,7 +10,7 @@ import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-OUT = os.path.join(CSRC, "librrt_b200.so")
+OUT = os.environ.get("RRT_OUT") or os.path.join(CSRC, "librrt_b200.so")   # RRT_OUT: variant builds (tools/)
 SOURCES = ["rrt_api.cu", "rrt_render.cu", "rrt_microbench.cu", "rrt_octree.cpp", "rrt_loader.cpp"]
 HEADERS = ["rrt_device.cuh", "rrt_trace.cuh", "rrt_shade.cuh", "rrt_render.h", "rrt_octree.h",
            os.path.join("..", "..", "include", "rrt.h")]
@@ -47,7 +47,7 @@ def build(force=False, verbose=False):
     cmd += [os.path.join(CSRC, s) for s in SOURCES] + ["-o", OUT]
     r = subprocess.run(cmd, capture_output=True, text=True)
     log = r.stdout + r.stderr
-    with open(os.path.join(CSRC, "build.log"), "w") as f:
+    with open(OUT[:-3] + ".log" if os.environ.get("RRT_OUT") else os.path.join(CSRC, "build.log"), "w") as f:
         f.write(" ".join(cmd) + "\n" + log)
     if r.returncode != 0:
         sys.stderr.write(log)

@@ -211,6 +211,11 @@ int rrt_scene_create(const rrt_scene_desc* d, int device, rrt_scene** out) {
     sc->dev.n_nodes = (uint32_t)flat.nodes.size();
     sc->dev.root_tri_count = st.n_tris_stored ? 1u : 0u;
     sc->dev.planes_safe = (flat.planes_safe && !std::getenv("RRT_SLOW_DIV")) ? 1u : 0u;
+#if RRT_CULL_F32
+    sc->dev.cull_o_max = kCullOriginRel * flat.scale;
+#else
+    sc->dev.cull_o_max = 0.0;
+#endif
 
     // shading records by original triangle id (entities.rs:78-84)
     {

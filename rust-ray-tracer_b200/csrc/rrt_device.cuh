@@ -33,7 +33,8 @@ struct DevScene {
     const DevTexture* tex;
     uint32_t n_nodes;
     uint32_t root_tri_count;   // nodes[0].triangle_count analogue: 0 => every ray misses (ray.rs:112-114)
-    uint32_t planes_safe;      // octree planes satisfy the range condition of the FMA quotient path
+    uint32_t planes_safe;      // octree planes satisfy the range/order conditions of the FMA quotient path
+    double cull_o_max;         // f32 culling: rays with an |origin component| above this are not culled
 };
 
 struct DevCounters {
@@ -71,9 +72,14 @@ __device__ __forceinline__ uint32_t rust_clamp_u8(double x) {
     return (uint32_t)x;
 }
 
+// What a traversal carries: t, the original triangle id (tie order, hit-id plane) and the record index.
+// u and v are NOT carried (4 registers per hit on a register-bound kernel): the closest-hit callers
+// re-evaluate them for the one winning record with hit_uv() — the same instruction sequence on the same
+// operands as the accepting test, hence the same bits.
 struct Hit {
-    double t, u, v;
+    double t;
     uint32_t id;      // original triangle index; UINT32_MAX = None
+    uint32_t rec;     // index of the winning DevTri record
 };
 
 // ---------------------------------------------------------------- Moller-Trumbore (ray.rs:56-94)
@@ -109,6 +115,20 @@ __device__ __forceinline__ bool moller_trumbore(const V3& o, const V3& d, const 
     if (!(t > kEps)) return false;             // ray.rs:89
     id = __double_as_longlong(r4.y) & 0xFFFFFFFFll;
     return true;
+}
+
+// u, v of an ACCEPTED record (ray.rs:60-80), bit-identical to what moller_trumbore computed for it.
+__device__ __forceinline__ void hit_uv(const V3& o, const V3& d, const DevTri* __restrict__ rec, double& u, double& v) {
+    const double2* p = reinterpret_cast<const double2*>(rec);
+    const double2 r0 = __ldg(p + 0), r1 = __ldg(p + 1), r2 = __ldg(p + 2), r3 = __ldg(p + 3), r4 = __ldg(p + 4);
+    const V3 v1{r0.x, r0.y, r1.x}, e1{r1.y, r2.x, r2.y}, e2{r3.x, r3.y, r4.x};
+    const V3 h = cross(d, e2);
+    const double a = dot(e1, h);
+    const double f = 1.0 / a;
+    const V3 s = o - v1;
+    u = f * dot(s, h);
+    const V3 q = cross(s, e1);
+    v = f * dot(d, q);
 }
 
 }  // namespace rrt

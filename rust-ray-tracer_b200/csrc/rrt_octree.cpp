@@ -139,7 +139,34 @@ struct CullBuilder {
     bool tight;                       // false: infinite boxes (culling off, every record is tested)
     uint32_t leaf_max;                // records per leaf (<= 8: 3-bit count field)
 
-    static void pad_box(double* b) {
+    double scale;                     // FlatScene::scale
+
+#if RRT_CULL_F32
+    void pad_box(double* b) const {
+        const double p = kCullPadRel * scale;
+        for (int k = 0; k < 3; ++k) {
+            b[k] -= p;
+            b[3 + k] += p;
+        }
+    }
+    static float down(double x) {
+        float f = (float)x;
+        if ((double)f > x) f = std::nextafterf(f, -INFINITY);
+        return f;
+    }
+    static float up(double x) {
+        float f = (float)x;
+        if ((double)f < x) f = std::nextafterf(f, INFINITY);
+        return f;
+    }
+    static void store_box(DevCull& c, int s, const double* b) {
+        for (int k = 0; k < 3; ++k) {
+            c.box[s][k] = down(b[k]);
+            c.box[s][3 + k] = up(b[3 + k]);
+        }
+    }
+#else
+    void pad_box(double* b) const {
         for (int k = 0; k < 3; ++k) {
             const double m = std::fmax(std::fabs(b[k]), std::fabs(b[3 + k]));
             const double p = 1e-7 * std::fmax(1.0, m);
@@ -147,8 +174,10 @@ struct CullBuilder {
             b[3 + k] += p;
         }
     }
+    static void store_box(DevCull& c, int s, const double* b) { std::memcpy(c.box[s], b, 6 * sizeof(double)); }
+#endif
     void bounds(uint32_t lo, uint32_t hi, double* b) const {
-        if (!tight) {
+        if (!tight || !(scale < INFINITY)) {
             for (int k = 0; k < 3; ++k) { b[k] = -INFINITY; b[3 + k] = INFINITY; }
             return;
         }
@@ -250,7 +279,7 @@ struct CullBuilder {
             const uint32_t n = r[s + 1] - r[s];
             const uint32_t child = (n <= leaf_max) ? leaf_word(rec_base + r[s], n) : build(r[s], r[s + 1], depth + 1);
             DevCull& c = out[me];  // re-fetch: vector may have grown
-            std::memcpy(c.box[s], b, sizeof b);
+            store_box(c, s, b);
             c.child[s] = child;
         }
         return me;
@@ -305,7 +334,21 @@ void flatten(const HostOctree& t, const double* v, uint32_t cull_threshold, Flat
                 const double p = k < 3 ? dn.px[k] : (k < 6 ? dn.py[k - 3] : dn.pz[k - 6]);
                 const double a = std::fabs(p);
                 if (!(p == 0.0 || (a >= std::ldexp(1.0, -400) && a < std::ldexp(1.0, 401)))) out->planes_safe = false;
+                // the sign-selected near/far planes of the fast path need min <= mid <= max on every axis
+                if (k % 3 != 0) {
+                    const double prev = k < 3 ? dn.px[k - 1] : (k < 6 ? dn.py[k - 4] : dn.pz[k - 7]);
+                    if (!(prev <= p)) out->planes_safe = false;
+                }
             }
+    // coordinate scale of everything a culling hierarchy can contain
+    out->scale = 1.0;
+    for (size_t d = 0; d < order.size(); ++d)
+        for (uint32_t tr = t.nodes[order[d]].head; tr != UINT32_MAX; tr = t.next[tr])
+            for (int k = 0; k < 9; ++k) {
+                const double a = std::fabs(v[9 * (size_t)tr + k]);
+                if (a > out->scale) out->scale = a;   // NaN / inf coordinates: see below
+            }
+    if (!(out->scale < 1e12)) out->scale = INFINITY;   // culling then pads to infinite boxes: every record is tested
     // triangle records, node by node
     std::vector<uint32_t> ids;
     for (size_t d = 0; d < order.size(); ++d) {
@@ -325,7 +368,7 @@ void flatten(const HostOctree& t, const double* v, uint32_t cull_threshold, Flat
             const bool tight = cull_threshold != 0;
             std::vector<double> boxes(6 * ids.size());
             for (size_t i = 0; i < ids.size(); ++i) tri_box(v + 9 * (size_t)ids[i], &boxes[6 * i]);
-            CullBuilder cb{v, ids, std::move(boxes), out->cull, dn.tri_first, tight, tight ? 4u : 8u};
+            CullBuilder cb{v, ids, std::move(boxes), out->cull, dn.tri_first, tight, tight ? 4u : 8u, out->scale};
             dn.cull_root = cb.build(0, (uint32_t)ids.size());
         }
         for (uint32_t id : ids) {

@@ -68,14 +68,33 @@ struct alignas(16) DevShade {
 };
 static_assert(sizeof(DevShade) == 128, "DevShade layout");
 
-// Culling hierarchy over one long node list (binary BVH, both child boxes in the parent). Boxes are
-// padded outward; every candidate it yields is still decided by the exact f64 Moller-Trumbore test.
+// Culling hierarchy over one long node list (binary BVH, both child boxes in the parent). Every candidate it
+// yields is still decided by the exact f64 Moller-Trumbore test; the boxes only have to be CONSERVATIVE.
+#ifndef RRT_CULL_F32
+#define RRT_CULL_F32 1
+#endif
+#if RRT_CULL_F32
+// f32 boxes, rounded outward after padding by kCullPadRel * S (S = scene coordinate scale, FlatScene::scale):
+// 64 bytes = 4 x 16-byte loads, tested with FP32 FFMA/FMNMX (full rate) instead of the FP64 pipe.
+// Error budget and the ray eligibility rule are in rrt_trace.cuh (CullRay).
+using cull_real = float;
 struct alignas(16) DevCull {
-    double box[2][6];     // child 0 / child 1 : min.xyz max.xyz (padded)
+    float box[2][6];      // child 0 / child 1 : min.xyz max.xyz (padded, rounded outward)
     uint32_t child[2];    // bit31 set: leaf = bit31 | (count-1) << 28 | first record; else index of DevCull
     uint32_t _pad[2];
 };
+static_assert(sizeof(DevCull) == 64, "DevCull layout");
+constexpr double kCullPadRel = 1e-5;
+constexpr double kCullOriginRel = 16.0;   // rays with |origin component| > kCullOriginRel * S are not culled
+#else
+using cull_real = double;
+struct alignas(16) DevCull {
+    double box[2][6];     // child 0 / child 1 : min.xyz max.xyz (padded by 1e-7 relative)
+    uint32_t child[2];
+    uint32_t _pad[2];
+};
 static_assert(sizeof(DevCull) == 112, "DevCull layout");
+#endif
 
 struct FlatScene {
     std::vector<DevNode> nodes;
@@ -83,7 +102,9 @@ struct FlatScene {
     std::vector<DevCull> cull;
     uint64_t n_stored = 0, root_list = 0, max_list = 0;
     uint32_t max_depth = 0;
-    bool planes_safe = true;   // every octree plane is 0 or has magnitude in [2^-400, 2^401) (rrt_trace.cuh)
+    bool planes_safe = true;   // every octree plane is 0 or has magnitude in [2^-400, 2^401), and the three planes
+                               // of every axis are ordered min <= mid <= max (rrt_trace.cuh)
+    double scale = 1.0;        // S = max(1, largest |coordinate| of a stored triangle): culling pad / eligibility unit
 };
 
 // Flatten: renumber kept nodes breadth-first (siblings consecutive), concatenate node lists.

@@ -39,7 +39,9 @@ render_kernel(const DevScene sc, const __grid_constant__ DevParams P, uint32_t* 
               DevCounters* __restrict__ counters, const int tiles_x, const unsigned long long total) {
     const unsigned lane = threadIdx.x & 31u;
     const unsigned lt_mask = (1u << lane) - 1u;
-    RayState st;
+    __shared__ double park_s[RRT_PARK ? kParkWords * kBlock : 1];
+    double* const park = park_s + (RRT_PARK ? threadIdx.x : 0);
+    RayStateT<kBlock> st;
     bool active = false, drained = false;
     size_t pix = 0;
     unsigned k = 0;
@@ -102,7 +104,7 @@ render_kernel(const DevScene sc, const __grid_constant__ DevParams P, uint32_t* 
         if (active) {
             Hit h;
             traverse<COUNT>(sc, st.so, st.sd, st.smax, st.shadow, h, tc_total);
-            if (st.advance<COUNT>(sc, P, h)) {
+            if (st.advance<COUNT>(sc, P, h, park)) {
                 active = false;
                 if (hit_ids) hit_ids[pix * 4 + k] = st.hit0;
                 const uint32_t c = st.res;
@@ -139,7 +141,9 @@ trace_kernel(const DevScene sc, const uint64_t n, const double* __restrict__ o, 
     traverse<false>(sc, V3{o[3 * i], o[3 * i + 1], o[3 * i + 2]}, V3{d[3 * i], d[3 * i + 1], d[3 * i + 2]}, mt, false, h, tc);
     out_tri[i] = (h.id == kNone) ? -1 : (int32_t)h.id;
     if (h.id != kNone && out_tuv) {
-        out_tuv[3 * i] = h.t; out_tuv[3 * i + 1] = h.u; out_tuv[3 * i + 2] = h.v;
+        double u, v;
+        hit_uv(V3{o[3 * i], o[3 * i + 1], o[3 * i + 2]}, V3{d[3 * i], d[3 * i + 1], d[3 * i + 2]}, sc.tris + h.rec, u, v);
+        out_tuv[3 * i] = h.t; out_tuv[3 * i + 1] = u; out_tuv[3 * i + 2] = v;
     }
 }
 
@@ -148,14 +152,16 @@ __global__ void __launch_bounds__(kBlock)
 colour_kernel(const DevScene sc, const __grid_constant__ DevParams P, const uint64_t n, const double* __restrict__ o,
               const double* __restrict__ d, uint8_t* __restrict__ out_rgb) {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    __shared__ double park_s[RRT_PARK ? kParkWords * kBlock : 1];
+    double* const park = park_s + (RRT_PARK ? threadIdx.x : 0);
     if (i >= n) return;
-    RayState st;
+    RayStateT<kBlock> st;
     TraceCount tc;
     st.begin(V3{o[3 * i], o[3 * i + 1], o[3 * i + 2]}, V3{d[3 * i], d[3 * i + 1], d[3 * i + 2]});
     Hit h;
     do {
         traverse<false>(sc, st.so, st.sd, st.smax, st.shadow, h, tc);
-    } while (!st.advance<false>(sc, P, h));
+    } while (!st.advance<false>(sc, P, h, park));
     const uint32_t c = st.res;
     out_rgb[3 * i] = (uint8_t)(c & 255u); out_rgb[3 * i + 1] = (uint8_t)((c >> 8) & 255u); out_rgb[3 * i + 2] = (uint8_t)((c >> 16) & 255u);
 }

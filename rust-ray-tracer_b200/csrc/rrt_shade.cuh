@@ -48,33 +48,44 @@ __device__ __forceinline__ void add_light(V3& I, const DevMaterial* __restrict__
     if (!spec) I = I + V3{0.0, 0.0, 0.0};
 }
 
+#ifndef RRT_PARK
+#define RRT_PARK 0
+#endif
+constexpr int kParkWords = 12;   // pt, n, I, view direction: the shading state that must survive a shadow traversal
+
 // Per-ray state of RayTracer::get_ray_colour_recursive (raytracer.rs:33-112) between traversals.
-// Usage:  st.begin(o, d);  do { traverse(st.so, st.sd, st.smax, st.shadow, h); } while (!st.advance(sc, P, h));
+// Usage:  st.begin(o, d);  do { traverse(st.so, st.sd, st.smax, st.shadow, h); } while (!st.advance(sc, P, h, park));
 // then st.res is the colour packed r | g<<8 | b<<16 and st.hit0 the depth-0 triangle id (-1 = miss).
-struct RayState {
+//
+// Register budget: the traversal is the hot loop and the kernel is register-bound (64 per thread), so the
+// only doubles this struct keeps in registers across a traversal are the ray handed to traverse().  The
+// shading state a shadow query interrupts (hit point, normal, accumulated light, view direction: 12
+// doubles) is PARKED in shared memory (`park`, one column per thread, stride kParkStride doubles) while
+// the shadow ray is traced, instead of letting the compiler spill whatever it picks to local memory.
+template <int kParkStride>
+struct RayStateT {
     // reflection stack: local colour and reflectivity of every open level (raytracer.rs:89-101)
     double lx[kMaxReflectDepth], ly[kMaxReflectDepth], lz[kMaxReflectDepth], lk[kMaxReflectDepth];
-    V3 ro, rd;            // current primary / reflection ray
-    V3 pt, n, I;          // hit point, shading normal, accumulated light (survive shadow traversals)
-    V3 so, sd;            // the ray to hand to traverse()
+    V3 so, sd;            // the ray to hand to traverse(); for primary / reflection rays it IS the current ray
     double smax;
-    const DevMaterial* mat;
+#if !RRT_PARK
+    double parked[kParkWords];
+#endif
     uint32_t texel, res;
-    int32_t hit0;
+    int32_t hit0, mid;    // depth-0 triangle id; material of the point being shaded
     int depth, li;
     bool shadow;
     RayCount rc;
 
     __device__ __forceinline__ void begin(const V3& o, const V3& d) {
-        ro = o; rd = d; so = o; sd = d;
+        so = o; sd = d;
         smax = __longlong_as_double(0x7FF0000000000000ll);
         shadow = false;
         depth = 0; li = 0;
         res = 0x00FFFFFFu;
         hit0 = -1;
-        mat = nullptr;
+        mid = 0;
         texel = 0;
-        pt = n = I = V3{0.0, 0.0, 0.0};
     }
 
     // unwind the open mirror levels: every level re-quantises to u8 (raytracer.rs:89-101)
@@ -88,9 +99,34 @@ struct RayState {
         }
     }
 
+    __device__ __forceinline__ void park_store(double* park, const V3& pt, const V3& n, const V3& I, const V3& rd) {
+#if RRT_PARK
+#define RRT_PK(i) park[(i) * kParkStride]
+#else
+#define RRT_PK(i) parked[i]
+        (void)park;
+#endif
+        RRT_PK(0) = pt.x; RRT_PK(1) = pt.y; RRT_PK(2) = pt.z;
+        RRT_PK(3) = n.x;  RRT_PK(4) = n.y;  RRT_PK(5) = n.z;
+        RRT_PK(6) = I.x;  RRT_PK(7) = I.y;  RRT_PK(8) = I.z;
+        RRT_PK(9) = rd.x; RRT_PK(10) = rd.y; RRT_PK(11) = rd.z;
+    }
+    __device__ __forceinline__ void park_load(const double* park, V3& pt, V3& n, V3& I, V3& rd) const {
+#if !RRT_PARK
+        (void)park;
+#endif
+        pt = V3{RRT_PK(0), RRT_PK(1), RRT_PK(2)};
+        n = V3{RRT_PK(3), RRT_PK(4), RRT_PK(5)};
+        I = V3{RRT_PK(6), RRT_PK(7), RRT_PK(8)};
+        rd = V3{RRT_PK(9), RRT_PK(10), RRT_PK(11)};
+#undef RRT_PK
+    }
+
     // Consumes the result of the traversal just made; returns true when the colour is final.
     template <bool COUNT>
-    __device__ __forceinline__ bool advance(const DevScene& sc, const DevParams& P, const Hit& h) {
+    __device__ __forceinline__ bool advance(const DevScene& sc, const DevParams& P, const Hit& h, double* park) {
+        V3 pt, n, I, rd;
+        const DevMaterial* __restrict__ mat;
         if (!shadow) {
             if (depth == 0) hit0 = (h.id == kNone) ? -1 : (int32_t)h.id;
             if (h.id == kNone) {  // WHITE raytracer.rs:109-111
@@ -99,24 +135,27 @@ struct RayState {
                 return true;
             }
             // ---- hit set-up (raytracer.rs:38-57)
+            rd = sd;
+            double hu, hv;
+            hit_uv(so, sd, sc.tris + h.rec, hu, hv);
             const double2* sp2 = reinterpret_cast<const double2*>(sc.shade + h.id);
             const double2 a0 = __ldg(sp2), a1 = __ldg(sp2 + 1), a2 = __ldg(sp2 + 2), a3 = __ldg(sp2 + 3),
                           a4 = __ldg(sp2 + 4), a5 = __ldg(sp2 + 5), a6 = __ldg(sp2 + 6), a7 = __ldg(sp2 + 7);
             const V3 n1{a0.x, a0.y, a1.x}, n2{a1.y, a2.x, a2.y}, n3{a3.x, a3.y, a4.x};
             const double t1x = a4.y, t1y = a5.x, t2x = a5.y, t2y = a6.x, t3x = a6.y, t3y = a7.x;
-            const int32_t mid = (int32_t)(__double_as_longlong(a7.y) & 0xFFFFFFFFll);
+            mid = (int32_t)(__double_as_longlong(a7.y) & 0xFFFFFFFFll);
             mat = sc.materials + mid;
-            pt = ro + rd * h.t;  // raytracer.rs:39
-            const double w = 1.0 - h.u - h.v;  // raytracer.rs:43
-            const double tex_x = t2x * h.u + t3x * h.v + t1x * w;  // raytracer.rs:45-47
-            const double tex_y = t2y * h.u + t3y * h.v + t1y * w;  // raytracer.rs:48-50
+            pt = so + sd * h.t;  // raytracer.rs:39
+            const double w = 1.0 - hu - hv;  // raytracer.rs:43
+            const double tex_x = t2x * hu + t3x * hv + t1x * w;  // raytracer.rs:45-47
+            const double tex_y = t2y * hu + t3y * hv + t1y * w;  // raytracer.rs:48-50
             const DevTexture tex = sc.tex[__ldg(&mat->tex)];
             const uint32_t tx = rust_usize_mod(tex_x * (double)tex.width, tex.width);    // raytracer.rs:52
             const uint32_t ty = rust_usize_mod(tex_y * (double)tex.height, tex.height);  // raytracer.rs:53
             const uchar4 c = __ldg(tex.texels + (size_t)tex.width * ty + tx);            // raytracer.rs:55
             texel = (uint32_t)c.x | ((uint32_t)c.y << 8) | ((uint32_t)c.z << 16);
             // ---- normal (raytracer.rs:114-162)
-            n = n2 * h.u + n3 * h.v + n1 * w;  // raytracer.rs:122-124
+            n = n2 * hu + n3 * hv + n1 * w;  // raytracer.rs:122-124
             const int32_t bump = __ldg(&mat->bump);
             if (bump >= 0) {
                 const DevTexture bt = sc.tex[bump];
@@ -136,6 +175,8 @@ struct RayState {
         } else {
             // result of the shadow query for point light `li` (raytracer.rs:232-252)
             shadow = false;
+            park_load(park, pt, n, I, rd);
+            mat = sc.materials + mid;
             if (h.id != kNone) {
                 li = P.n_lights;  // `break`: ends the WHOLE light loop (raytracer.rs:235-237)
             } else {
@@ -158,6 +199,7 @@ struct RayState {
                 li++;
             } else {
                 // triangle_exists_between_points (raytracer.rs:164-188)
+                park_store(park, pt, n, I, rd);
                 sd = V3{L.vec[0], L.vec[1], L.vec[2]} - pt;  // raytracer.rs:170
                 so = pt + n * P.offset;                     // raytracer.rs:172
                 smax = length(sd);                          // raytracer.rs:179
@@ -174,11 +216,10 @@ struct RayState {
         if (kr > 0.0 && depth < P.max_depth) {  // raytracer.rs:76
             const double d_dot_n = dot(rd, n);  // raytracer.rs:78
             const V3 ndir = normalised(rd - n * 2.0 * d_dot_n);  // raytracer.rs:79
-            ro = pt + n * P.offset;  // raytracer.rs:82
-            rd = ndir;
+            so = pt + n * P.offset;  // raytracer.rs:82
+            sd = ndir;
             lx[depth] = local.x; ly[depth] = local.y; lz[depth] = local.z; lk[depth] = kr;
             depth++;
-            so = ro; sd = rd;
             smax = __longlong_as_double(0x7FF0000000000000ll);
             if (COUNT) rc.reflect++;
             return false;

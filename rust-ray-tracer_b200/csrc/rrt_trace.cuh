@@ -32,10 +32,14 @@ __device__ __forceinline__ double max_nn(double a, double b) { return b > a ? b 
 //         checked here, and every octree plane in {0} U [2^-400, 2^401), checked at flatten time
 //         (DevScene::planes_safe) — so a = plane - o is 0 or has magnitude in [2^-452, 2^402], every
 //         quotient is normal and every residual a - d*q is representable (a multiple of 2^(e_a-104)).
+//         The three planes of an axis are ordered p0 <= p1 <= p2 (also part of planes_safe), subtraction
+//         and correctly rounded division are monotone, so q0 <= q1 <= q2 for d > 0 and q0 >= q1 >= q2
+//         for d < 0: the min/max of ray.rs:29-36 over a pair of plane quotients is a SELECT on the sign
+//         of d (equal quotients make either choice the same value).
 //   otherwise (zero / tiny / huge / non-finite component): true divisions and NaN-aware min/max.
 struct AxisRay {
     double o, d, y;
-    bool fast;
+    bool fast, neg;
 };
 
 __device__ __forceinline__ bool safe_mag(double x, bool zero_ok) {
@@ -48,6 +52,7 @@ __device__ __forceinline__ AxisRay make_axis(double o, double d, bool planes_saf
     a.o = o;
     a.d = d;
     a.fast = planes_safe && safe_mag(d, false) && safe_mag(o, true);
+    a.neg = d < 0.0;
     a.y = 1.0 / d;
     return a;
 }
@@ -78,14 +83,23 @@ static __device__ __noinline__ void slab_axis_slow(double p0, double p1, double 
     out[3] = mx1 != mx1 ? pinf : mx1;
 }
 
+#ifndef RRT_SLAB_SIGN
+#define RRT_SLAB_SIGN 1
+#endif
+
 // mn[h] / mx[h] = min / max of the two plane quotients bounding half h (0 = low, 1 = high) of one axis.
 __device__ __forceinline__ void slab_axis(const AxisRay& a, double p0, double p1, double p2, double& mn0, double& mn1,
                                           double& mx0, double& mx1) {
     if (a.fast) {
         const double a0 = p0 - a.o, a1 = p1 - a.o, a2 = p2 - a.o;
         const double q0 = div_markstein(a0, a.d, a.y), q1 = div_markstein(a1, a.d, a.y), q2 = div_markstein(a2, a.d, a.y);
+#if RRT_SLAB_SIGN
+        mn0 = a.neg ? q1 : q0; mx0 = a.neg ? q0 : q1;
+        mn1 = a.neg ? q2 : q1; mx1 = a.neg ? q1 : q2;
+#else
         mn0 = min_nn(q0, q1); mx0 = max_nn(q0, q1);
         mn1 = min_nn(q1, q2); mx1 = max_nn(q1, q2);
+#endif
     } else {
         double out[4];
         slab_axis_slow(p0, p1, p2, a.o, a.d, out);
@@ -93,18 +107,84 @@ __device__ __forceinline__ void slab_axis(const AxisRay& a, double p0, double p1
     }
 }
 
+// ---------------------------------------------------------------- conservative culling of long lists
+// The hierarchy's boxes only decide which records get the exact test, so they are tested in FP32 (FFMA +
+// FMNMX at full rate, 64-byte nodes) with everything rounded or padded to the safe side.
+// Error budget, in units of S = FlatScene::scale (>= 1, >= every |coordinate| of a stored triangle):
+//   * boxes are padded by 1e-5 S, then rounded outward to f32;
+//   * a ray is ELIGIBLE when every |origin component| <= 16 S and max|direction component| is in
+//     [1e-10, 1e10] (anything else — NaN included — is not culled at all: every record is tested);
+//   * per plane t~ = fma(b, inv, -(o32*inv)), o32 = RN32(o), inv = RN32(1/d) clamped to +-1e25:
+//     |o - o32| <= 2^-24 * 16 S, the product o32*inv and the fma each round once (2^-24 relative to
+//     terms of magnitude <= 17 S |inv|), inv carries 2^-24 relative: in space units the plane moves by
+//     less than 4.2e-6 S, under half of the pad.  A hit accepted by the exact test lies within 1e-12 S of
+//     its triangle, hence (pad) strictly inside the computed slab interval on every axis:
+//     tnear~ <= t* <= tfar~, which is all the three comparisons below use (t* > 0; `tnear~ > nb.t` proves
+//     t* > nb.t, so an exact tie is never pruned).
+//   * a direction component that is zero or below 1e-25 uses inv = +-1e25: the ray cannot leave a slab of
+//     thickness >= 2 pad within t <= 17 S / 1e-10, and the computed interval is either astronomically
+//     wide around 0 (origin inside) or astronomically far on one side (origin outside by > pad/2).
+#if RRT_CULL_F32
+struct CullRay {
+    float ix, iy, iz, cx, cy, cz;   // inv and -(o32 * inv)
+    bool ok;
+};
+__device__ __forceinline__ CullRay make_cull_ray(const DevScene& sc, const V3& o, const V3& d, const AxisRay& ax,
+                                                 const AxisRay& ay, const AxisRay& az) {
+    CullRay c;
+    const double m = fmax(fmax(fabs(d.x), fabs(d.y)), fabs(d.z));
+    c.ok = fabs(o.x) <= sc.cull_o_max && fabs(o.y) <= sc.cull_o_max && fabs(o.z) <= sc.cull_o_max && m >= 1e-10 &&
+           m <= 1e10 && d.x == d.x && d.y == d.y && d.z == d.z;
+    c.ix = fminf(fmaxf(__double2float_rn(ax.y), -1e25f), 1e25f);
+    c.iy = fminf(fmaxf(__double2float_rn(ay.y), -1e25f), 1e25f);
+    c.iz = fminf(fmaxf(__double2float_rn(az.y), -1e25f), 1e25f);
+    c.cx = -(__double2float_rn(o.x) * c.ix);
+    c.cy = -(__double2float_rn(o.y) * c.iy);
+    c.cz = -(__double2float_rn(o.z) * c.iz);
+    return c;
+}
+// one child box of a DevCull: returns "may contain an acceptable hit with t <= limit", tnear out
+__device__ __forceinline__ bool cull_box(const CullRay& c, float bx0, float by0, float bz0, float bx1, float by1, float bz1,
+                                         float limit, float& tnear) {
+    const float x0 = fmaf(bx0, c.ix, c.cx), x1 = fmaf(bx1, c.ix, c.cx);
+    const float y0 = fmaf(by0, c.iy, c.cy), y1 = fmaf(by1, c.iy, c.cy);
+    const float z0 = fmaf(bz0, c.iz, c.cz), z1 = fmaf(bz1, c.iz, c.cz);
+    tnear = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fminf(z0, z1));
+    const float tfar = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fmaxf(z0, z1));
+    return !c.ok || ((tnear <= tfar) && (tfar >= 0.0f) && (tnear <= limit));
+}
+#endif
+
+// ray.rs:39-46: hit = !(tmax < 0.0) && !(tmin > tmax), as `bit` or 0.  Written as two chained predicate
+// compares: left to the compiler the pair is rewritten into an IEEE fmax(tmin, 0) (NaN quieting and all,
+// 8 instructions per child box) followed by a compare.
+__device__ __forceinline__ uint32_t slab_hit_bit(double tmin, double tmax, uint32_t bit) {
+    uint32_t r;
+    asm("{\n\t.reg .pred p;\n\tsetp.geu.f64 p, %1, 0d0000000000000000;\n\tsetp.leu.and.f64 p, %2, %1, p;\n\t"
+        "selp.u32 %0, %3, 0, p;\n\t}"
+        : "=r"(r)
+        : "d"(tmax), "d"(tmin), "r"(bit));
+    return r;
+}
+
 // One exact triangle test against the node-local best: strict '<', and on an exact t tie the earlier
 // list entry wins (ray.rs:123-127). Lists are in ascending triangle id, so "earlier" == smaller id;
 // records may therefore be visited in any order.
-__device__ __forceinline__ void test_record(const V3& o, const V3& d, const DevTri* rec, Hit& nb) {
+__device__ __forceinline__ bool test_record(const V3& o, const V3& d, const DevTri* __restrict__ tris, uint32_t r, Hit& nb) {
     double t, u, v;
     uint32_t id;
-    if (moller_trumbore(o, d, rec, t, u, v, id)) {
+    if (moller_trumbore(o, d, tris + r, t, u, v, id)) {
         if (t < nb.t || (t == nb.t && nb.id != kNone && id < nb.id)) {
-            nb.t = t; nb.u = u; nb.v = v; nb.id = id;
+            nb.t = t; nb.id = id; nb.rec = r;
+            return true;
         }
     }
+    return false;
 }
+
+#ifndef RRT_CULL_LOOP
+#define RRT_CULL_LOOP 0   // 0: if leaf / else inner per iteration; 1: inner step then leaf step; 2: descend-until-leaf
+#endif
 
 // Ray::intersect_with_octant_with_max_t(octree, 0, max_t).  any_hit: the caller only needs Some/None
 // (shadow rays, raytracer.rs:181-187) — `best` only ever improves, so the first update decides.
@@ -112,49 +192,68 @@ template <bool COUNT>
 __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const V3& d, const double max_t,
                                          const bool any_hit, Hit& best, TraceCount& tc) {
     best.id = kNone;
+    best.rec = 0;
     best.t = max_t;
-    best.u = 0.0;
-    best.v = 0.0;
     if (sc.root_tri_count == 0) return;  // ray.rs:112-114 at the root
 
-    uint2 stk[kMaxOctreeDepth + 1];  // per level: .x = first kept child, .y = remaining order (3 bits each) | count << 24
+    // Open levels of the walk: the deepest one lives in registers (lv_first = first kept child of the node,
+    // lv_ord = remaining visiting order, 3 bits per child, | remaining count << 24); shallower levels that
+    // still have children left are on the stack.  Exhausted levels are never pushed.
+    uint2 stk[kMaxOctreeDepth + 1];
+    uint32_t lv_first = 0, lv_ord = 0;
     uint32_t cstk[kMaxCullDepth + 2];  // culling-hierarchy stack (depth bounded by the builder)
     int sp = 0;
     uint32_t node = 0;
     bool is_root = true;
     const AxisRay ax = make_axis(o.x, d.x, sc.planes_safe != 0u), ay = make_axis(o.y, d.y, sc.planes_safe != 0u),
                   az = make_axis(o.z, d.z, sc.planes_safe != 0u);
+    const double kInf = __longlong_as_double(0x7FF0000000000000ll);
+#if RRT_CULL_F32
+    const CullRay cr = make_cull_ray(sc, o, d, ax, ay, az);
+#else
     // reciprocal direction for the CONSERVATIVE culling boxes only (never for a reference decision)
     const double ivx = min_nn(max_nn(ax.y, -1e300), 1e300), ivy = min_nn(max_nn(ay.y, -1e300), 1e300),
                  ivz = min_nn(max_nn(az.y, -1e300), 1e300);
-    const double kInf = __longlong_as_double(0x7FF0000000000000ll);
+#endif
 
     for (;;) {
         const DevNode* __restrict__ n = sc.nodes + node;
         const uint4 m = __ldg(reinterpret_cast<const uint4*>(&n->first_child));  // first_child, child_mask, tri_first, tri_n
         if (COUNT) tc.nodes++;
 
-        // ---- own triangles (ray.rs:116-129): one loop for linear lists, hierarchy nodes and their leaves
+        // ---- own triangles (ray.rs:116-129): hierarchy nodes and their leaves; a short list is one leaf word
         Hit nb;
         nb.id = kNone;
+        nb.rec = 0;
         nb.t = is_root ? max_t : kInf;
-        nb.u = nb.v = 0.0;
         if (m.w != 0u) {
             uint32_t cur = __ldg(&n->cull_root);
             int csp = 0;
-            for (;;) {
-                if (cur & kLeafBit) {
-                    const DevTri* rec = sc.tris + (cur & 0x0FFFFFFFu);
-                    const uint32_t cnt = ((cur >> 28) & 7u) + 1u;
-                    for (uint32_t i = 0; i < cnt; ++i) {
-                        if (COUNT) tc.mt++;
-                        test_record(o, d, rec + i, nb);
-                    }
-                    if (any_hit && nb.id != kNone && nb.t < best.t) break;  // best will improve => Some
-                    if (csp == 0) break;
-                    cur = cstk[--csp];
-                } else {
+            bool live = true;
+#if RRT_CULL_F32
+            float limit = __double2float_ru(nb.t);
+#endif
+            while (live) {
+#if RRT_CULL_LOOP == 2
+                while (live && !(cur & kLeafBit)) {
+#elif RRT_CULL_LOOP == 1
+                if (!(cur & kLeafBit)) {
+#else
+                const bool was_leaf = (cur & kLeafBit) != 0u;
+                if (!was_leaf) {
+#endif
                     const DevCull* __restrict__ c = sc.cull + cur;
+                    bool go0, go1, swap;
+                    if (COUNT) tc.cull += 2;
+#if RRT_CULL_F32
+                    const float4* bp = reinterpret_cast<const float4*>(c);
+                    const float4 f0 = __ldg(bp), f1 = __ldg(bp + 1), f2 = __ldg(bp + 2);
+                    const uint2 ch = __ldg(reinterpret_cast<const uint2*>(&c->child[0]));
+                    float tn0, tn1;
+                    go0 = cull_box(cr, f0.x, f0.y, f0.z, f0.w, f1.x, f1.y, limit, tn0);
+                    go1 = cull_box(cr, f1.z, f1.w, f2.x, f2.y, f2.z, f2.w, limit, tn1);
+                    swap = tn1 < tn0;
+#else
                     const double2* bp = reinterpret_cast<const double2*>(c);
                     const uint2 ch = __ldg(reinterpret_cast<const uint2*>(&c->child[0]));
                     bool go[2];
@@ -162,7 +261,6 @@ __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const 
 #pragma unroll
                     for (int s = 0; s < 2; ++s) {
                         const double2 b0 = __ldg(bp + 3 * s), b1 = __ldg(bp + 3 * s + 1), b2 = __ldg(bp + 3 * s + 2);
-                        if (COUNT) tc.cull++;
                         const double x0 = (b0.x - o.x) * ivx, x1 = (b1.y - o.x) * ivx;
                         const double y0 = (b0.y - o.y) * ivy, y1 = (b2.x - o.y) * ivy;
                         const double z0 = (b1.x - o.z) * ivz, z1 = (b2.y - o.z) * ivz;
@@ -174,21 +272,44 @@ __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const 
                         go[s] = (tnear <= tfar) && (tfar >= 0.0) && (tnear <= nb.t);
                         tn[s] = tnear;
                     }
-                    if (go[0] && go[1]) {
-                        const bool swap = tn[1] < tn[0];
+                    go0 = go[0]; go1 = go[1];
+                    swap = tn[1] < tn[0];
+#endif
+                    if (go0 && go1) {
                         cstk[csp++] = swap ? ch.x : ch.y;
                         cur = swap ? ch.y : ch.x;
-                    } else if (go[0] || go[1]) {
-                        cur = go[0] ? ch.x : ch.y;
-                    } else {
-                        if (csp == 0) break;
+                    } else if (go0 || go1) {
+                        cur = go0 ? ch.x : ch.y;
+                    } else if (csp != 0) {
                         cur = cstk[--csp];
+                    } else {
+                        live = false;
                     }
+                }
+#if RRT_CULL_LOOP == 0
+                if (was_leaf) {
+#else
+                if (live && (cur & kLeafBit)) {
+#endif
+                    const uint32_t first = cur & 0x0FFFFFFFu;
+                    const uint32_t cnt = ((cur >> 28) & 7u) + 1u;
+                    bool upd = false;
+                    for (uint32_t i = 0; i < cnt; ++i) {
+                        if (COUNT) tc.mt++;
+                        upd |= test_record(o, d, sc.tris, first + i, nb);
+                    }
+                    if (any_hit && nb.id != kNone && nb.t < best.t) break;  // best will improve => Some
+#if RRT_CULL_F32
+                    if (upd) limit = __double2float_ru(nb.t);
+#endif
+                    if (csp != 0) cur = cstk[--csp];
+                    else live = false;
                 }
             }
         }
         if (nb.id != kNone) {
             sp = 0;  // this node returns Some: every pending sibling, at every level, is dead
+            lv_ord = 0;
             if (nb.t < best.t) {
                 best = nb;
                 if (any_hit) return;
@@ -206,21 +327,28 @@ __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const 
             slab_axis(ax, q0.x, q0.y, q1.x, mnx[0], mnx[1], mxx[0], mxx[1]);
             slab_axis(ay, q1.y, q2.x, q2.y, mny[0], mny[1], mxy[0], mxy[1]);
             slab_axis(az, q3.x, q3.y, q4, mnz[0], mnz[1], mxz[0], mxz[1]);
+            // max(max(x, y), z) / min(min(x, y), z) of ray.rs:29-36: the (x, y) part is shared by the two
+            // children that differ only in z
+            double nxy[2][2], fxy[2][2];
+#pragma unroll
+            for (int xh = 0; xh < 2; ++xh)
+#pragma unroll
+                for (int yh = 0; yh < 2; ++yh) {
+                    nxy[xh][yh] = max_nn(mnx[xh], mny[yh]);
+                    fxy[xh][yh] = min_nn(mxx[xh], mxy[yh]);
+                }
             double key[8];
             uint32_t hitmask = 0;
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
-                key[k] = 0.0;
-                if ((m.y >> k) & 1u) {
-                    const int xh = (k == 2 || k == 3 || k == 6 || k == 7) ? 1 : 0, yh = k >= 4 ? 1 : 0,
-                              zh = (k == 1 || k == 2 || k == 5 || k == 6) ? 1 : 0;
-                    const double tmin = max_nn(max_nn(mnx[xh], mny[yh]), mnz[zh]);  // ray.rs:29-32
-                    const double tmax = min_nn(min_nn(mxx[xh], mxy[yh]), mxz[zh]);  // ray.rs:33-36
-                    const bool hit = !(tmax < 0.0) && !(tmin > tmax);               // ray.rs:39-46
-                    key[k] = (tmin < 0.0) ? tmax : tmin;                             // ray.rs:49-53
-                    hitmask |= hit ? (1u << k) : 0u;
-                }
+                const int xh = (k == 2 || k == 3 || k == 6 || k == 7) ? 1 : 0, yh = k >= 4 ? 1 : 0,
+                          zh = (k == 1 || k == 2 || k == 5 || k == 6) ? 1 : 0;
+                const double tmin = max_nn(nxy[xh][yh], mnz[zh]);  // ray.rs:29-32
+                const double tmax = min_nn(fxy[xh][yh], mxz[zh]);  // ray.rs:33-36
+                key[k] = (tmin < 0.0) ? tmax : tmin;                 // ray.rs:49-53
+                hitmask |= slab_hit_bit(tmin, tmax, 1u << k);        // ray.rs:39-46
             }
+            hitmask &= m.y;
             if (COUNT) tc.box += __popc(m.y);
             if (hitmask) {
                 // stable sort by key (ray.rs:146-147) as repeated selection of the smallest remaining key,
@@ -242,17 +370,21 @@ __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const 
                 }
                 const uint32_t last = (uint32_t)__ffs(rem) - 1u;
                 order |= (uint32_t)__popc(m.y & ((1u << last) - 1u)) << shift;
-                stk[sp++] = make_uint2(m.x, order | (nh << 24));
+                if (lv_ord >> 24) stk[sp++] = make_uint2(lv_first, lv_ord);
+                lv_first = m.x;
+                lv_ord = order | (nh << 24);
             }
         }
 
         // ---- next node: first remaining child of the deepest open level (ray.rs:152-161)
-        while (sp > 0 && (stk[sp - 1].y >> 24) == 0u) --sp;
-        if (sp == 0) return;
-        const uint2 top = stk[sp - 1];
-        node = top.x + (top.y & 7u);
-        const uint32_t cnt = (top.y >> 24) - 1u;
-        stk[sp - 1].y = ((top.y & 0x00FFFFFFu) >> 3) | (cnt << 24);
+        if ((lv_ord >> 24) == 0u) {
+            if (sp == 0) return;
+            const uint2 top = stk[--sp];
+            lv_first = top.x;
+            lv_ord = top.y;
+        }
+        node = lv_first + (lv_ord & 7u);
+        lv_ord = ((lv_ord & 0x00FFFFFFu) >> 3) | (((lv_ord >> 24) - 1u) << 24);
         is_root = false;
     }
 }
