@@ -36,7 +36,12 @@ int cuda_fail(cudaError_t e, const char* what) {
 uint32_t cull_threshold() {
     const char* s = std::getenv("RRT_CULL_THRESHOLD");
     if (s && *s) return (uint32_t)std::strtoul(s, nullptr, 10);
-    return 8;
+    return 1;
+}
+uint32_t cull_leaf() {
+    const char* s = std::getenv("RRT_CULL_LEAF");
+    if (s && *s) return (uint32_t)std::strtoul(s, nullptr, 10);
+    return 1;
 }
 
 }  // namespace
@@ -188,7 +193,7 @@ int rrt_scene_create(const rrt_scene_desc* d, int device, rrt_scene** out) {
     std::string err;
     if (!tree.build(d->v, d->n_tris, d->root_min, d->root_max, &err)) return fail(RRT_ERR_DEPTH, err);
     FlatScene flat;
-    flatten(tree, d->v, cull_threshold(), &flat);
+    flatten(tree, d->v, cull_threshold(), cull_leaf(), &flat);
 
     auto sc = std::make_unique<rrt_scene>();
     sc->device = device;

@@ -288,7 +288,7 @@ struct CullBuilder {
 
 }  // namespace
 
-void flatten(const HostOctree& t, const double* v, uint32_t cull_threshold, FlatScene* out) {
+void flatten(const HostOctree& t, const double* v, uint32_t cull_threshold, uint32_t cull_leaf, FlatScene* out) {
     out->nodes.clear();
     out->tris.clear();
     out->cull.clear();
@@ -360,15 +360,31 @@ void flatten(const HostOctree& t, const double* v, uint32_t cull_threshold, Flat
         out->n_stored += ids.size();
         if (hi == 0) out->root_list = ids.size();
         else out->max_list = std::max<uint64_t>(out->max_list, ids.size());
+        for (int k = 0; k < 3; ++k) { dn.list_box[k] = -INFINITY; dn.list_box[3 + k] = INFINITY; }
+#if RRT_CULL_F32
+        if (!ids.empty() && cull_threshold != 0 && out->scale < INFINITY) {
+            double b[6], tb[6];
+            for (int k = 0; k < 3; ++k) { b[k] = INFINITY; b[3 + k] = -INFINITY; }
+            for (uint32_t id : ids) {
+                tri_box(v + 9 * (size_t)id, tb);
+                for (int k = 0; k < 3; ++k) { b[k] = std::fmin(b[k], tb[k]); b[3 + k] = std::fmax(b[3 + k], tb[3 + k]); }
+            }
+            const double pad = kCullPadRel * out->scale;
+            for (int k = 0; k < 3; ++k) {
+                dn.list_box[k] = CullBuilder::down(b[k] - pad);
+                dn.list_box[3 + k] = CullBuilder::up(b[3 + k] + pad);
+            }
+        }
+#endif
         if (ids.empty()) {
             dn.cull_root = UINT32_MAX;
-        } else if (ids.size() <= 8) {
+        } else if (ids.size() <= (cull_threshold ? std::min(cull_threshold, 8u) : 8u)) {
             dn.cull_root = CullBuilder::leaf_word(dn.tri_first, (uint32_t)ids.size());  // short list: one leaf
         } else {
             const bool tight = cull_threshold != 0;
             std::vector<double> boxes(6 * ids.size());
             for (size_t i = 0; i < ids.size(); ++i) tri_box(v + 9 * (size_t)ids[i], &boxes[6 * i]);
-            CullBuilder cb{v, ids, std::move(boxes), out->cull, dn.tri_first, tight, tight ? 4u : 8u, out->scale};
+            CullBuilder cb{v, ids, std::move(boxes), out->cull, dn.tri_first, tight, tight ? std::max(1u, std::min(cull_leaf, 8u)) : 8u, out->scale};
             dn.cull_root = cb.build(0, (uint32_t)ids.size());
         }
         for (uint32_t id : ids) {

@@ -37,18 +37,21 @@ struct HostOctree {
 // ---------------------------------------------------------------- device layout
 
 // Node kept on the device (only nodes with triangle_count > 0; empty ones return None at ray.rs:112
-// and the child sort is stable, so dropping them cannot change a result).  96 bytes.
-struct alignas(16) DevNode {
+// and the child sort is stable, so dropping them cannot change a result).  128 bytes = one cache line.
+struct alignas(128) DevNode {
     uint32_t first_child;        // device index of the first kept child (kept children are consecutive)
     uint32_t child_mask;         // bit k = reference child k (order octree.rs:216-225) is kept
     uint32_t tri_first, tri_n;   // own triangle records [tri_first, tri_first + tri_n)
     double px[3], py[3], pz[3];  // the 3 planes per axis shared by the 8 child boxes: min, min+half, max
                                  // (octree.rs:136-210) — 9 distinct slab numerators instead of 48
     uint32_t cull_root;          // entry of this list's culling hierarchy: a DevCull index, or a leaf word
-                                 // (bit31 | (count-1) << 28 | first record) when the list has <= 8 records
+                                 // (bit31 | (count-1) << 28 | first record) when the list is short
     uint32_t _pad;
+    float list_box[6];           // conservative (padded, outward-rounded) f32 box of the node's OWN list:
+                                 // a ray that misses it cannot be accepted by any record of the list
+    uint32_t _pad2[2];
 };
-static_assert(sizeof(DevNode) == 96, "DevNode layout");
+static_assert(sizeof(DevNode) == 128, "DevNode layout");
 
 // Intersection record, 80 bytes = 5 x 16-byte vector loads. e1/e2 are the reference's own
 // `v2 - v1`, `v3 - v1` (ray.rs:60-61) evaluated once on the host in f64: same operands, same bits.
@@ -108,9 +111,10 @@ struct FlatScene {
 };
 
 // Flatten: renumber kept nodes breadth-first (siblings consecutive), concatenate node lists.
-// cull_threshold: lists longer than this get a culling hierarchy with tight (padded) boxes.
+// cull_threshold (1..8): lists longer than this get a culling hierarchy with tight (padded) boxes whose
+// leaves hold at most cull_leaf (1..8) records; shorter lists are one leaf (every record is tested).
 // 0 = culling off: long lists still go through the same hierarchy code, but with infinite boxes, so
 // every record of the list is tested (the exact linear scan of the reference, in another order).
-void flatten(const HostOctree& t, const double* v, uint32_t cull_threshold, FlatScene* out);
+void flatten(const HostOctree& t, const double* v, uint32_t cull_threshold, uint32_t cull_leaf, FlatScene* out);
 
 }  // namespace rrt

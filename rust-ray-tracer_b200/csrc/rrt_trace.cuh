@@ -182,6 +182,9 @@ __device__ __forceinline__ bool test_record(const V3& o, const V3& d, const DevT
     return false;
 }
 
+#ifndef RRT_LIST_BOX
+#define RRT_LIST_BOX 1
+#endif
 #ifndef RRT_CULL_LOOP
 #define RRT_CULL_LOOP 0   // 0: if leaf / else inner per iteration; 1: inner step then leaf step; 2: descend-until-leaf
 #endif
@@ -226,13 +229,25 @@ __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const 
         nb.id = kNone;
         nb.rec = 0;
         nb.t = is_root ? max_t : kInf;
+#if RRT_CULL_F32
+        float limit = __double2float_ru(nb.t);
+        bool scan = m.w != 0u;
+#if RRT_LIST_BOX
+        if (scan) {  // the node's own list as a whole
+            const float4 lb = __ldg(reinterpret_cast<const float4*>(&n->list_box[0]));
+            const float2 lc = __ldg(reinterpret_cast<const float2*>(&n->list_box[4]));
+            float tn;
+            if (COUNT) tc.cull++;
+            scan = cull_box(cr, lb.x, lb.y, lb.z, lb.w, lc.x, lc.y, limit, tn);
+        }
+#endif
+        if (scan) {
+#else
         if (m.w != 0u) {
+#endif
             uint32_t cur = __ldg(&n->cull_root);
             int csp = 0;
             bool live = true;
-#if RRT_CULL_F32
-            float limit = __double2float_ru(nb.t);
-#endif
             while (live) {
 #if RRT_CULL_LOOP == 2
                 while (live && !(cur & kLeafBit)) {
