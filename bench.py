@@ -254,9 +254,10 @@ def run_gpu(args):
             cpu, per_ray = None, cpu_baseline(sd, p, target_seconds=2.0)[1]   # counters only
         flops_ray, bytes_ray = algorithmic_work(per_ray)
         rays_launch = 4 * W * sr.n_local
-        traffic = None
+        traffic, prof = None, {}
         try:
-            traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(args.workload)
+            prof = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+            traffic = prof.get(args.workload)
         except OSError:
             pass
         a_tf = flops_ray * rays_launch / (kern_ms * 1e-3) / 1e12
@@ -281,6 +282,16 @@ def run_gpu(args):
                                  "most of that work through conservative culling, so frac may exceed 1; executed work below.",
                          "kernel_ms": kern_ms, "algorithmic_flops_per_ray": flops_ray, "algorithmic_bytes_per_ray": bytes_ray,
                          "reference_work_per_ray": per_ray, "executed_per_ray": executed},
+            # what the kernel itself pushes through the FP64 pipe (ncu opcode counts of the committed profile of
+            # this workload, whole launch on one GPU) over the live kernel time, against the same measured peak
+            "executed_fp64": (None if world != 1 or (args.workload + "_fp64_lane_inst") not in prof else {
+                "lane_inst_per_launch": prof[args.workload + "_fp64_lane_inst"],
+                "achieved": prof[args.workload + "_fp64_lane_inst"] / (kern_ms * 1e-3) / 1e12, "peak": fp64.value,
+                "unit": "T lane-inst/s (DADD/DMUL/DFMA/DSETP, one per lane)",
+                "frac": prof[args.workload + "_fp64_lane_inst"] / (kern_ms * 1e-3) / 1e12 / fp64.value,
+                "issue_active_pct": prof.get(args.workload + "_issue_active_pct"),
+                "fp64_pipe_active_pct": prof.get(args.workload + "_fp64_pipe_active_pct"),
+                "source": "profiles/traffic.json"}),
             "roofline_hbm": {"bound": "hbm", "achieved": a_gb, "peak": hbm_peak, "unit": "GB/s", "frac": a_gb / hbm_peak,
                              "peak_source": hbm_src, "traffic": traffic,
                              "note": "algorithmic bytes are cache-level (scene is L2-resident); not the limiter"},
