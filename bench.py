@@ -30,15 +30,19 @@ WORKLOADS = {
     "c1": ("model2.obj at the reference's default window (BASELINE configs[0])", 800, 800),
     "c3a": ("model.obj textured/bump scene (BASELINE configs[2])", 1920, 1080),
     "c3b": ("model3.obj textured/bump scene (BASELINE configs[2])", 1920, 1080),
+    # configs[4]: every step is the next frame of the 64-frame camera orbit (rotation = documented extension)
+    "c5": ("synthetic 10,000,000-triangle soup, 64-frame camera orbit (BASELINE configs[4])", 7680, 4320),
 }
 
 
 def load_workload(name):
     import rrt_b200  # noqa: F401
     from rrt_b200.loader import load_scene_npz
-    from rrt_b200.synthetic import sphere_grid
+    from rrt_b200.synthetic import sphere_grid, triangle_soup
     if name == "c4":
         return sphere_grid()
+    if name == "c5":
+        return triangle_soup()
     fixture = {"c2": "model2", "c1": "model2", "c3a": "model", "c3b": "model3"}[name]
     return load_scene_npz(os.path.join(ROOT, "tests", "golden", "scenes", fixture + ".npz"))
 
@@ -191,8 +195,18 @@ def run_gpu(args):
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)      # max over ranks
         return float(ms.item())
 
+    step_no = [0]
+
+    def step_params():
+        """c5: frame k of the orbit; every other workload: the reference camera."""
+        if args.workload != "c5":
+            return p
+        origin, rot = rrt_b200.orbit_camera(step_no[0] % 64)
+        step_no[0] += 1
+        return rt.params(W, H, origin=origin, camera_rot=rot)
+
     def frame():
-        sr.render(p)
+        sr.render(step_params())
         sr.assemble()
 
     for _ in range(Wm):
@@ -204,7 +218,8 @@ def run_gpu(args):
     value = rays_frame * K / (total_ms * 1e-3) / 1e6
 
     # dominant kernel alone (render_kernel on this rank's shard), same hygiene
-    kern_ms = timed_steps(K, lambda: sr.render(p)) / K
+    step_no[0] = 0
+    kern_ms = timed_steps(K, lambda: sr.render(step_params())) / K
 
     # ---- end to end through the public API with HOST buffers (pinned), copies inside the timed region
     host = torch.empty((H, W), dtype=torch.int32, pin_memory=True)
@@ -214,7 +229,12 @@ def run_gpu(args):
 
     def e2e_step():
         if world == 1:
-            scene.draw_scene(rt)               # rrt_render: params H2D (kernel args) + kernel + frame D2H
+            if args.workload == "c5":
+                origin, rot = rrt_b200.orbit_camera(step_no[0] % 64)
+                step_no[0] += 1
+                scene.draw_scene(rt, origin=origin, camera_rot=rot)
+            else:
+                scene.draw_scene(rt)           # rrt_render: params H2D (kernel args) + kernel + frame D2H
         else:
             frame()
             if rank == 0:

@@ -103,3 +103,37 @@ def test_camera_rotation_extension_matches_oracle(rrt, scenes):
     check_frame(rrt, scenes("model2"), 160, 90, origin=origin, camera_rot=rot)
     o0, r0 = rrt.orbit_camera(0)
     assert r0 is None and o0 == (0.0, 2.0, -10.0)
+
+
+def test_config5_geometry_small_soup_orbit(rrt):
+    # config[4] geometry at a size the oracle renders in full: seeded triangle soup, three orbit frames
+    from rrt_b200.synthetic import triangle_soup
+    sd = triangle_soup(20000, size=0.4)
+    for k in (0, 5, 23):
+        origin, rot = rrt.orbit_camera(k)
+        fb, hit, ofb, ohit = check_frame(rrt, sd, 160, 90, origin=origin, camera_rot=rot)
+        assert np.array_equal(hit, ohit) and (hit >= 0).mean() > 0.3
+
+
+def test_rays_outside_the_f32_culling_range_bit_exact(rrt, scenes):
+    # the f32 culling boxes are only used for rays whose origin is within 16 scene scales and whose largest
+    # direction component is in [1e-10, 1e10]; everything else must take the uncull'd path and still match
+    from oracle.oracle import OracleScene
+    sd = scenes("model2")
+    rt, o = rrt.RayTracer(sd), OracleScene(sd)
+    rng = np.random.default_rng(5)
+    n = 6000
+    target = rng.uniform(-4, 4, (n, 3)) + np.array([0.0, 2.0, 0.0])
+    d = rng.normal(size=(n, 3))
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    dist = np.repeat([5.0, 300.0, 330.0, 1e4, 1e7, 20.0], n // 6)          # 20*16 = 320 is the eligibility edge
+    org = target - d * dist[:, None]
+    scale = np.tile([1.0, 1e-12, 1e12, 1e-9, 1e9, 1e-200], n // 6)          # direction magnitudes around the limits
+    d = d * scale[:, None]
+    d[::11, 0] = 0.0
+    tri, tuv = rt.intersect_with_octant_with_max_t(org, d)
+    otri, otuv = o.trace(org, d)
+    assert np.array_equal(tri, otri)
+    assert np.array_equal(tuv[tri >= 0], otuv[otri >= 0])
+    assert (tri >= 0).sum() > 1000
+    rt.close()

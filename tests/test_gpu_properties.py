@@ -96,3 +96,29 @@ def test_fma_quotient_path_equals_division_path(rrt, scenes, monkeypatch):
     fb2, hit2 = render(rrt, rt2, 960, 540, hits=True)
     assert np.array_equal(fb, fb2) and np.array_equal(hit, hit2)
     rt.close(); rt2.close()
+
+
+def test_config5_full_size_lattice_against_oracle(rrt):
+    # config[4] at FULL size (10M-triangle soup, 7680x4320), orbit frame 5: the oracle cannot render the frame
+    # (a ray scans an 82,834-triangle root list), so it renders a 96-pixel lattice of it; hit ids and pixels
+    # must be identical there, and the frame must be idempotent.
+    from oracle.oracle import OracleScene
+    from rrt_b200.synthetic import triangle_soup
+    sd = triangle_soup()
+    rt = rrt.RayTracer(sd)
+    st = rt.stats()
+    assert st["n_tris_stored"] == 10_000_000 and st["root_list"] > 50_000
+    W, H = 7680, 4320
+    origin, rot = rrt.orbit_camera(5)
+    sc = rrt.Scene(W, H)
+    fb = sc.draw_scene(rt, want_hit_ids=True, origin=origin, camera_rot=rot).copy()
+    hit = sc.hit_ids
+    fb2 = sc.draw_scene(rt, origin=origin, camera_rot=rot)
+    assert np.array_equal(fb, fb2) and (fb[0] == 0).all()
+    step = 96
+    ofb, ohit, _, _ = OracleScene(sd).render(rt.params(W, H, origin=origin, camera_rot=rot), row_step=step, col_step=step)
+    rows, cols = np.arange(1, H, step), np.arange(0, W, step)
+    assert np.array_equal(hit[np.ix_(rows, cols)], ohit[np.ix_(rows, cols)])
+    assert np.array_equal(fb[np.ix_(rows, cols)], ofb[np.ix_(rows, cols)])
+    assert (ohit[np.ix_(rows, cols)] >= 0).mean() > 0.9
+    rt.close()
