@@ -157,10 +157,13 @@ def run_gpu(args):
         raise SystemExit("no CUDA device for this rank: the renderer has no CPU fallback")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    # stdout carries exactly ONE JSON line: NCCL (version banner, NCCL_DEBUG output) and anything else a library
+    # prints at the C level is sent to stderr for the whole run; the line itself goes to the saved descriptor.
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-            os.environ["NCCL_DEBUG"] = "WARN"      # keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=dev)
 
     desc, W, H = WORKLOADS[args.workload]
@@ -170,7 +173,7 @@ def run_gpu(args):
     build_s = time.time() - t0
     stats = rt.stats()
     p = rt.params(W, H)
-    sr = ShardedRenderer(rt, W, H, rank, world, tile_rows=DEFAULT_TILE_ROWS)
+    sr = ShardedRenderer(rt, W, H, rank, world, tile_rows=DEFAULT_TILE_ROWS, assemble=args.assemble)
     flush = torch.empty(256 << 20, dtype=torch.int8, device=dev)      # > 126 MB L2
     stream = torch.cuda.current_stream(dev)
     K, Wm = args.steps, args.warmup
@@ -287,14 +290,16 @@ def run_gpu(args):
             "steps": K, "warmup": Wm, "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": f"{args.workload}: {desc} at {W}x{H}", "n_tris": int(sd.n_tris),
-                       "parallelism": f"interleaved tile rows x{world} (tile_rows={DEFAULT_TILE_ROWS}), scene replicated, "
-                                      "all-gather + de-interleave per frame" if world > 1 else "single GPU",
+                       "parallelism": (f"interleaved tile rows x{world} (tile_rows={DEFAULT_TILE_ROWS}), scene replicated, " +
+                                       ("render kernels store finished pixels into rank 0's frame over NVLink peer memory"
+                                        if sr.mode == "peer" else "NCCL all-gather + de-interleave per frame"))
+                       if world > 1 else "single GPU",
                        "l2": "flushed (256 MB write) between timed iterations", "octree": stats,
                        "scene_build_s": round(build_s, 2)},
             "clocks": clocks,
             "e2e": {"value": e2e_val, "unit": "Mrays/s", "h2d_bytes_per_step": C.sizeof(abi.RenderParams),
                     "d2h_bytes_per_step": W * H * 4, "ms_per_step": float(e2e_ms.item()) / K},
-            "gpu_launches": K * (1 + (1 if world > 1 else 0)),
+            "gpu_launches": K * (1 + (1 if world > 1 and sr.mode == "nccl" else 0)),
             "roofline": {"bound": "fp64", "kernel": "render_kernel", "achieved": a_tf, "peak": fp64.value,
                          "unit": "TFLOP/s", "frac": a_tf / fp64.value, "traffic": traffic,
                          "note": "achieved = REFERENCE-executed flops/ray (SURVEY 8d formula, oracle counters) x rays per launch / "
@@ -318,7 +323,14 @@ def run_gpu(args):
         }
         if cpu is not None:
             line["cpu_baseline"] = {k: cpu[k] for k in ("value", "unit", "cores", "kind", "sample")}
-        print(json.dumps(line), flush=True)
+        sys.stdout.flush()
+        os.write(json_fd, (json.dumps(line) + "\n").encode())
+    if world > 1:                 # peers unmap rank 0's frame before rank 0 frees it
+        if rank != 0:
+            sr.close()
+        dist.barrier()
+        if rank == 0:
+            sr.close()
     rt.close()
     if world > 1:
         dist.barrier()
@@ -332,6 +344,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS))
+    ap.add_argument("--assemble", default="peer", choices=["peer", "nccl"],
+                    help="N>1 frame assembly: peer = render kernels store into rank 0's frame over NVLink (CUDA IPC); "
+                         "nccl = all-gather of compact rows + de-interleave")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="size of the bounded CPU-baseline sample")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":

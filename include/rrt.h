@@ -171,6 +171,25 @@ int rrt_render(rrt_scene* scene, const rrt_render_params* params,
 int rrt_render_device(rrt_scene* scene, const rrt_render_params* params, const rrt_shard* shard,
                       uint32_t* d_fb, int32_t* d_hit_ids, void* cuda_stream);
 
+/* Fused render + gather: the shard's rows are stored straight into a FULL frame (row r of the frame at
+ * d_frame[r*width ...], reference layout), which may live on ANOTHER GPU: a pointer obtained from
+ * rrt_ipc_open_handle() on a frame a peer process allocated with rrt_frame_alloc().  Every pixel is
+ * written once, 4 bytes, by the lane that finishes its 4th supersample; pixel stores of different
+ * shards never overlap, so no ordering is needed beyond "all ranks' kernels have completed" (a barrier
+ * on the callers' streams).  Replaces per frame: gather of compact rows + rrt_deinterleave_device. */
+int rrt_render_device_into_frame(rrt_scene* scene, const rrt_render_params* params, const rrt_shard* shard,
+                                 uint32_t* d_frame, void* cuda_stream);
+
+/* Frame buffers that can be shared between the one-process-per-GPU ranks of a node (CUDA IPC over
+ * NVLink peer access).  handle = 64 opaque bytes (cudaIpcMemHandle_t) to send to the peers. */
+int rrt_frame_alloc(int device, int32_t width, int32_t height, uint32_t** d_frame);
+int rrt_frame_free(int device, uint32_t* d_frame);
+int rrt_ipc_get_handle(int device, const void* d_ptr, unsigned char handle[64]);
+int rrt_ipc_open_handle(int device, const unsigned char handle[64], void** d_ptr);
+int rrt_ipc_close_handle(int device, void* d_ptr);
+int rrt_copy_frame_to_host(int device, const uint32_t* d_frame, int32_t width, int32_t height,
+                           uint32_t* fb_0rgb, void* cuda_stream);   /* async on the stream if fb is pinned */
+
 /* Number of buffer rows shard `shard_index` owns for a frame of `height` rows (row 0 included). */
 int rrt_shard_rows(int32_t height, const rrt_shard* shard);
 

@@ -77,6 +77,8 @@ SYMBOLS = [
     "rrt_abi_version", "rrt_last_error", "rrt_device_count", "rrt_render_params_default",
     "rrt_scene_create", "rrt_scene_destroy", "rrt_scene_get_stats",
     "rrt_render", "rrt_render_device", "rrt_shard_rows", "rrt_deinterleave_device",
+    "rrt_render_device_into_frame", "rrt_frame_alloc", "rrt_frame_free", "rrt_ipc_get_handle", "rrt_ipc_open_handle",
+    "rrt_ipc_close_handle", "rrt_copy_frame_to_host",
     "rrt_trace_rays", "rrt_ray_colours", "rrt_render_counters",
     "rrt_octree_build", "rrt_octree_destroy", "rrt_octree_node_count", "rrt_octree_node", "rrt_octree_node_list",
     "rrt_obj_load", "rrt_obj_destroy", "rrt_obj_n_tris", "rrt_obj_v", "rrt_obj_vt", "rrt_obj_vn",
@@ -108,6 +110,13 @@ def lib():
     L.rrt_scene_get_stats.argtypes = [vp, C.POINTER(SceneStats)]
     L.rrt_render.argtypes = [vp, C.POINTER(RenderParams), vp, vp, C.POINTER(C.c_float)]
     L.rrt_render_device.argtypes = [vp, C.POINTER(RenderParams), C.POINTER(Shard), vp, vp, vp]
+    L.rrt_render_device_into_frame.argtypes = [vp, C.POINTER(RenderParams), C.POINTER(Shard), vp, vp]
+    L.rrt_frame_alloc.argtypes = [C.c_int, i32, i32, C.POINTER(vp)]
+    L.rrt_frame_free.argtypes = [C.c_int, vp]
+    L.rrt_ipc_get_handle.argtypes = [C.c_int, vp, vp]
+    L.rrt_ipc_open_handle.argtypes = [C.c_int, vp, C.POINTER(vp)]
+    L.rrt_ipc_close_handle.argtypes = [C.c_int, vp]
+    L.rrt_copy_frame_to_host.argtypes = [C.c_int, vp, i32, i32, vp, vp]
     L.rrt_shard_rows.argtypes = [i32, C.POINTER(Shard)]
     L.rrt_deinterleave_device.argtypes = [C.c_int, vp, i32, i32, i32, i32, i32, vp, vp]
     L.rrt_trace_rays.argtypes = [vp, u64, vp, vp, vp, vp, vp]

@@ -313,6 +313,64 @@ int rrt_render_device(rrt_scene* s, const rrt_render_params* p, const rrt_shard*
     return RRT_OK;
 }
 
+int rrt_render_device_into_frame(rrt_scene* s, const rrt_render_params* p, const rrt_shard* shard, uint32_t* d_frame,
+                                 void* cuda_stream) {
+    if (!s || !d_frame) return fail(RRT_ERR_INVALID, "null argument");
+    DevParams P;
+    int rc = make_params(p, shard, &P);
+    if (rc) return rc;
+    P.full_frame = 1;
+    CU(cudaSetDevice(s->device));
+    if ((rc = ensure(&s->d_scratch, &s->scratch_cap, render_scratch_words(P.n_rows_local, P.W)))) return rc;
+    CU(launch_render(s->dev, P, d_frame, nullptr, s->d_scratch, nullptr, (cudaStream_t)cuda_stream));
+    return RRT_OK;
+}
+
+int rrt_frame_alloc(int device, int32_t width, int32_t height, uint32_t** d_frame) {
+    if (!d_frame || width <= 0 || height <= 0) return fail(RRT_ERR_INVALID, "bad argument");
+    CU(cudaSetDevice(device));
+    void* p = nullptr;
+    CU(cudaMalloc(&p, (size_t)width * height * sizeof(uint32_t)));   // its own allocation: IPC handles export whole allocations
+    CU(cudaMemset(p, 0, (size_t)width * height * sizeof(uint32_t)));
+    *d_frame = (uint32_t*)p;
+    return RRT_OK;
+}
+int rrt_frame_free(int device, uint32_t* d_frame) {
+    CU(cudaSetDevice(device));
+    if (d_frame) CU(cudaFree(d_frame));
+    return RRT_OK;
+}
+int rrt_ipc_get_handle(int device, const void* d_ptr, unsigned char handle[64]) {
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t size");
+    if (!d_ptr || !handle) return fail(RRT_ERR_INVALID, "null argument");
+    CU(cudaSetDevice(device));
+    cudaIpcMemHandle_t h;
+    CU(cudaIpcGetMemHandle(&h, const_cast<void*>(d_ptr)));
+    std::memcpy(handle, &h, 64);
+    return RRT_OK;
+}
+int rrt_ipc_open_handle(int device, const unsigned char handle[64], void** d_ptr) {
+    if (!d_ptr || !handle) return fail(RRT_ERR_INVALID, "null argument");
+    CU(cudaSetDevice(device));
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, handle, 64);
+    CU(cudaIpcOpenMemHandle(d_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return RRT_OK;
+}
+int rrt_ipc_close_handle(int device, void* d_ptr) {
+    CU(cudaSetDevice(device));
+    if (d_ptr) CU(cudaIpcCloseMemHandle(d_ptr));
+    return RRT_OK;
+}
+int rrt_copy_frame_to_host(int device, const uint32_t* d_frame, int32_t width, int32_t height, uint32_t* fb,
+                           void* cuda_stream) {
+    if (!d_frame || !fb || width <= 0 || height <= 0) return fail(RRT_ERR_INVALID, "bad argument");
+    CU(cudaSetDevice(device));
+    CU(cudaMemcpyAsync(fb, d_frame, (size_t)width * height * sizeof(uint32_t), cudaMemcpyDeviceToHost,
+                       (cudaStream_t)cuda_stream));
+    return RRT_OK;
+}
+
 int rrt_render(rrt_scene* s, const rrt_render_params* p, uint32_t* fb, int32_t* hit_ids, float* device_ms) {
     if (!s || !fb) return fail(RRT_ERR_INVALID, "null argument");
     DevParams P;

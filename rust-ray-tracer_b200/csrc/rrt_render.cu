@@ -43,7 +43,7 @@ render_kernel(const DevScene sc, const __grid_constant__ DevParams P, uint32_t* 
     double* const park = park_s + (RRT_PARK ? threadIdx.x : 0);
     RayStateT<kBlock> st;
     bool active = false, drained = false;
-    size_t pix = 0;
+    size_t pix = 0, out = 0;   // compact pixel index (accumulator, hit ids) / index the finished pixel is stored at
     unsigned k = 0;
     TraceCount tc_total;
     uint32_t n_primary = 0, n_shadow = 0, n_reflect = 0;
@@ -71,6 +71,7 @@ render_kernel(const DevScene sc, const __grid_constant__ DevParams P, uint32_t* 
                     if (col < P.W && krow < P.n_rows_local) {
                         pix = (size_t)krow * P.W + col;
                         const int r = buffer_row(P, krow);
+                        out = P.full_frame ? (size_t)r * P.W + col : pix;
                         // put_pixel: new_x = x + W/2, new_y = H - (y + H/2)  (engine.rs:147-150)
                         const int x = col - P.W / 2;
                         const int y = P.H - r - P.H / 2;
@@ -90,7 +91,7 @@ render_kernel(const DevScene sc, const __grid_constant__ DevParams P, uint32_t* 
                         } else {
                             // never written by the reference (row 0, odd last column / row): stays 0, hit id -1
                             if (hit_ids) hit_ids[pix * 4 + k] = -1;
-                            if ((atomicAdd(acc + pix, 1u << 30) >> 30) == 3u) fb[pix] = 0u;
+                            if ((atomicAdd(acc + pix, 1u << 30) >> 30) == 3u) fb[out] = 0u;
                         }
                     }
                 }
@@ -113,7 +114,7 @@ render_kernel(const DevScene sc, const __grid_constant__ DevParams P, uint32_t* 
                 if ((old >> 30) == 3u) {  // 4th sample of this pixel: Color::mix + pack (entities.rs:32-36,49-69)
                     const uint32_t sum = old + add;
                     const uint32_t r = (sum & 1023u) >> 2, g = ((sum >> 10) & 1023u) >> 2, b = ((sum >> 20) & 1023u) >> 2;
-                    fb[pix] = b + (g << 8) + (r << 16);
+                    fb[out] = b + (g << 8) + (r << 16);
                 }
             }
         }

@@ -122,3 +122,81 @@ def test_config5_full_size_lattice_against_oracle(rrt):
     assert np.array_equal(fb[np.ix_(rows, cols)], ofb[np.ix_(rows, cols)])
     assert (ohit[np.ix_(rows, cols)] >= 0).mean() > 0.9
     rt.close()
+
+
+def test_fused_render_into_full_frame_equals_whole(rrt, scenes):
+    # rrt_render_device_into_frame: every shard stores its rows straight into ONE full frame (what the ranks
+    # do over NVLink peer memory at N > 1); here the shards run one after another on one GPU.
+    import torch
+    sd = scenes("model2")
+    rt = rrt.RayTracer(sd)
+    W, H = 1000, 562
+    whole, _ = render(rrt, rt, W, H)
+    p = rt.params(W, H)
+    L = rrt.abi.lib()
+    for G, T in ((2, 8), (3, 5), (8, 8)):
+        fp = C.c_void_p()
+        rrt.abi.check(L.rrt_frame_alloc(0, W, H, C.byref(fp)))
+        for r in range(G):
+            sh = rrt.abi.Shard(T, G, r)
+            rrt.abi.check(L.rrt_render_device_into_frame(rt.handle, C.byref(p), C.byref(sh), fp, None))
+        out = np.empty((H, W), dtype=np.uint32)
+        rrt.abi.check(L.rrt_copy_frame_to_host(0, fp, W, H, out.ctypes.data, None))
+        torch.cuda.synchronize()
+        assert np.array_equal(out, whole)
+        rrt.abi.check(L.rrt_frame_free(0, fp))
+    rt.close()
+
+
+def _peer_worker(rank, world, port, q):
+    import torch
+    import torch.distributed as dist
+    import rrt_b200
+    from rrt_b200.loader import load_scene_npz
+    from rrt_b200.sharding import ShardedRenderer
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    sd = load_scene_npz(os.path.join(os.path.dirname(__file__), "golden", "scenes", "model2.npz"))
+    rt = rrt_b200.RayTracer(sd, device=rank)
+    W, H = 640, 360
+    p = rt.params(W, H)
+    out = {}
+    for mode in ("peer", "nccl"):
+        sr = ShardedRenderer(rt, W, H, rank, world, tile_rows=8, assemble=mode)
+        for _ in range(2):
+            sr.render(p)
+            f = sr.assemble()
+        torch.cuda.synchronize()
+        if rank == 0:
+            out[mode] = f.cpu().numpy().view(np.uint32).copy()
+        if rank != 0:
+            sr.close()
+        dist.barrier()
+        if rank == 0:
+            sr.close()
+    if rank == 0:
+        sc = rrt_b200.Scene(W, H)
+        out["whole"] = sc.draw_scene(rt).copy()
+        q.put(out)
+    rt.close()
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_peer_frame_two_gpus(rrt):
+    # N = 2, one process per GPU: rank 1's render kernel stores into rank 0's frame through CUDA IPC / NVLink
+    import torch
+    import torch.multiprocessing as mp
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_peer_worker, args=(r, 2, 29541, q)) for r in range(2)]
+    for pr in procs:
+        pr.start()
+    out = q.get(timeout=300)
+    for pr in procs:
+        pr.join(timeout=120)
+        assert pr.exitcode == 0
+    assert np.array_equal(out["peer"], out["whole"]) and np.array_equal(out["nccl"], out["whole"])
