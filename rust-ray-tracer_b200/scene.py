@@ -168,7 +168,11 @@ class RayTracer:
             abi.lib().rrt_scene_destroy(self._h)
             self._h = None
 
-    __del__ = close
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:      # interpreter shutdown
+            pass
 
     @property
     def handle(self):
