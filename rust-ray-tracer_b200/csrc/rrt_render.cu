@@ -13,6 +13,10 @@ namespace {
 #ifndef RRT_MIN_BLOCKS
 #define RRT_MIN_BLOCKS 8
 #endif
+#ifndef RRT_REFILL_MIN
+#define RRT_REFILL_MIN 32    // idle lanes a warp waits for before it fetches new samples; 32 = a warp keeps one 4x2-pixel
+                             // tile (x4 supersamples) together through its shadow / mirror rays (sweep: profiles/r01_experiments.md)
+#endif
 constexpr int kBlock = RRT_BLOCK;
 constexpr int kTileW = 16;       // samples are enumerated in 16x4-pixel blocks of eight 4x2-pixel tiles,
 constexpr int kTileH = 4;        // 4 supersamples per pixel: 32 consecutive indices = one 8x4 half-pixel lattice
@@ -51,7 +55,7 @@ render_kernel(const DevScene sc, const __grid_constant__ DevParams P, uint32_t* 
     for (;;) {
         // ---- refill idle lanes from the global sample queue
         const unsigned idle = __ballot_sync(0xFFFFFFFFu, !active);
-        if (idle && !drained) {
+        if (__popc(idle) >= RRT_REFILL_MIN && !drained) {
             const int leader = __ffs(idle) - 1;
             unsigned long long base = 0;
             if ((int)lane == leader) base = atomicAdd(next, (unsigned long long)__popc(idle));
