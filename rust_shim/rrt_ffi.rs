@@ -51,9 +51,22 @@ extern "C" {
     pub fn rrt_scene_destroy(scene: *mut rrt_scene);
     pub fn rrt_render(scene: *mut rrt_scene, params: *const rrt_render_params, fb_0rgb: *mut u32,
                       hit_ids: *mut i32, device_ms: *mut f32) -> c_int;
-    pub fn rrt_render_device(scene: *mut rrt_scene, params: *const rrt_render_params, shard: *const c_void,
+    pub fn rrt_render_device(scene: *mut rrt_scene, params: *const rrt_render_params, shard: *const rrt_shard,
                              d_fb: *mut u32, d_hit_ids: *mut i32, cuda_stream: *mut c_void) -> c_int;
+    // multi-GPU: fused render + gather into a (possibly peer-mapped) full frame, include/rrt.h
+    pub fn rrt_render_device_into_frame(scene: *mut rrt_scene, params: *const rrt_render_params,
+                                        shard: *const rrt_shard, d_frame: *mut u32, cuda_stream: *mut c_void) -> c_int;
+    pub fn rrt_frame_alloc(device: c_int, width: i32, height: i32, d_frame: *mut *mut u32) -> c_int;
+    pub fn rrt_frame_free(device: c_int, d_frame: *mut u32) -> c_int;
+    pub fn rrt_ipc_get_handle(device: c_int, d_ptr: *const c_void, handle: *mut u8 /* [64] */) -> c_int;
+    pub fn rrt_ipc_open_handle(device: c_int, handle: *const u8 /* [64] */, d_ptr: *mut *mut c_void) -> c_int;
+    pub fn rrt_ipc_close_handle(device: c_int, d_ptr: *mut c_void) -> c_int;
+    pub fn rrt_copy_frame_to_host(device: c_int, d_frame: *const u32, width: i32, height: i32, fb_0rgb: *mut u32,
+                                  cuda_stream: *mut c_void) -> c_int;
 }
+
+/// rrt_shard (include/rrt.h): tile row j of `tile_rows` scan-lines belongs to shard j % n_shards.
+#[repr(C)] pub struct rrt_shard { pub tile_rows: i32, pub n_shards: i32, pub shard_index: i32 }
 
 pub fn last_error() -> String {
     unsafe { std::ffi::CStr::from_ptr(rrt_last_error()).to_string_lossy().into_owned() }
