@@ -123,6 +123,7 @@ typedef struct rrt_scene_stats {
     uint64_t max_list;         /* longest non-root node list                        */
     uint64_t n_cull_nodes;     /* nodes of the per-list culling hierarchies         */
     uint64_t device_bytes;     /* bytes resident in HBM for this scene              */
+    uint64_t flat_digest;      /* FNV-1a of the flattened node / record / culling arrays (rrt_octree_flatten_stats only) */
 } rrt_scene_stats;
 
 /* Per-frame work counters summed over all rays (optional; see rrt_render_counters). */
@@ -222,6 +223,9 @@ uint64_t rrt_octree_node_count(const rrt_octree* t);
  * (0 = leaf; children are 8 consecutive nodes, octree.rs:226-237), list length. */
 int rrt_octree_node(const rrt_octree* t, uint64_t i, double box[6], uint64_t* triangle_count,
                     uint64_t* first_child, uint64_t* list_len);
+/* Host-only: flatten the tree into the device layout (what rrt_scene_create uploads) and report its
+ * statistics, a digest of the arrays and the seconds it took.  v = the triangle array the tree was built from. */
+int rrt_octree_flatten_stats(const rrt_octree* t, const double* v, rrt_scene_stats* out, double* seconds);
 /* Copies node i's triangle list (insertion order, octree.rs:78,91,103) into out[0..cap). Returns length. */
 int64_t rrt_octree_node_list(const rrt_octree* t, uint64_t i, uint32_t* out, uint64_t cap);
 

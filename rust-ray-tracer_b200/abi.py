@@ -57,7 +57,7 @@ class Shard(C.Structure):
 class SceneStats(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in
                 ("n_tris", "n_tris_stored", "n_tris_dropped", "n_nodes", "n_nodes_nonempty", "max_depth",
-                 "root_list", "max_list", "n_cull_nodes", "device_bytes")]
+                 "root_list", "max_list", "n_cull_nodes", "device_bytes", "flat_digest")]
 
     def as_dict(self):
         return {n: int(getattr(self, n)) for n, _ in self._fields_}
@@ -81,6 +81,7 @@ SYMBOLS = [
     "rrt_ipc_close_handle", "rrt_copy_frame_to_host",
     "rrt_trace_rays", "rrt_ray_colours", "rrt_render_counters",
     "rrt_octree_build", "rrt_octree_destroy", "rrt_octree_node_count", "rrt_octree_node", "rrt_octree_node_list",
+    "rrt_octree_flatten_stats",
     "rrt_obj_load", "rrt_obj_destroy", "rrt_obj_n_tris", "rrt_obj_v", "rrt_obj_vt", "rrt_obj_vn",
     "rrt_obj_material_id", "rrt_obj_n_materials", "rrt_obj_materials", "rrt_obj_material_name",
     "rrt_obj_n_textures", "rrt_obj_texture_name", "rrt_write_ppm", "rrt_microbench_fp64", "rrt_selftest_division",
@@ -128,6 +129,7 @@ def lib():
     L.rrt_octree_node_count.argtypes = [vp]
     L.rrt_octree_node_count.restype = u64
     L.rrt_octree_node.argtypes = [vp, u64, dp, C.POINTER(u64), C.POINTER(u64), C.POINTER(u64)]
+    L.rrt_octree_flatten_stats.argtypes = [vp, vp, C.POINTER(SceneStats), dp]
     L.rrt_octree_node_list.argtypes = [vp, u64, vp, u64]
     L.rrt_octree_node_list.restype = C.c_int64
     L.rrt_obj_load.argtypes = [C.c_char_p, C.c_char_p, C.POINTER(vp)]

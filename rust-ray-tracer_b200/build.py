@@ -18,7 +18,7 @@ HEADERS = ["rrt_device.cuh", "rrt_trace.cuh", "rrt_shade.cuh", "rrt_render.h", "
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-fmad=false", "-prec-div=true", "-prec-sqrt=true", "-ftz=false",
-    "-Xcompiler", "-fPIC,-O2,-ffp-contract=off,-fno-fast-math,-Wall",
+    "-Xcompiler", "-fPIC,-O2,-ffp-contract=off,-fno-fast-math,-Wall,-fopenmp", "-lgomp",
     "-Xptxas", "-v",
 ]
 

@@ -1,5 +1,6 @@
 // rrt_api.cu — the C ABI of include/rrt.h: scene upload, render calls, per-ray seams.
 // No CPU rendering path exists in this library: every render entry point needs a CUDA device.
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -490,6 +491,35 @@ int rrt_octree_node(const rrt_octree* t, uint64_t i, double box[6], uint64_t* tr
     if (triangle_count) *triangle_count = n.triangle_count;
     if (first_child) *first_child = n.first_child;
     if (list_len) *list_len = n.list_len;
+    return RRT_OK;
+}
+int rrt_octree_flatten_stats(const rrt_octree* t, const double* v, rrt_scene_stats* out, double* seconds) {
+    if (!t || !out || (t->t.n_tris && !v)) return fail(RRT_ERR_INVALID, "null argument");
+    const auto t0 = std::chrono::steady_clock::now();
+    FlatScene flat;
+    flatten(t->t, v, cull_threshold(), cull_leaf(), &flat);
+    if (seconds) *seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    std::memset(out, 0, sizeof *out);
+    out->n_tris = t->t.n_tris;
+    out->n_tris_stored = flat.n_stored;
+    out->n_tris_dropped = t->t.n_dropped;
+    out->n_nodes = t->t.nodes.size();
+    out->n_nodes_nonempty = (t->t.nodes[0].triangle_count > 0) ? flat.nodes.size() : 0;
+    out->max_depth = t->t.max_depth;
+    out->root_list = flat.root_list;
+    out->max_list = flat.max_list;
+    out->n_cull_nodes = flat.cull.size();
+    out->device_bytes = flat.nodes.size() * sizeof(DevNode) + flat.tris.size() * sizeof(DevTri) + flat.cull.size() * sizeof(DevCull);
+    // order-independent digest of the flattened arrays, so tests can compare builds (e.g. 1 thread vs many)
+    uint64_t h = 1469598103934665603ull;
+    auto mix = [&h](const void* p, size_t n) {
+        const unsigned char* b = static_cast<const unsigned char*>(p);
+        for (size_t i = 0; i < n; ++i) { h ^= b[i]; h *= 1099511628211ull; }
+    };
+    mix(flat.nodes.data(), flat.nodes.size() * sizeof(DevNode));
+    mix(flat.tris.data(), flat.tris.size() * sizeof(DevTri));
+    mix(flat.cull.data(), flat.cull.size() * sizeof(DevCull));
+    out->flat_digest = h;
     return RRT_OK;
 }
 int64_t rrt_octree_node_list(const rrt_octree* t, uint64_t i, uint32_t* out, uint64_t cap) {

@@ -349,55 +349,88 @@ void flatten(const HostOctree& t, const double* v, uint32_t cull_threshold, uint
                 if (a > out->scale) out->scale = a;   // NaN / inf coordinates: see below
             }
     if (!(out->scale < 1e12)) out->scale = INFINITY;   // culling then pads to infinite boxes: every record is tested
-    // triangle records, node by node
-    std::vector<uint32_t> ids;
-    for (size_t d = 0; d < order.size(); ++d) {
-        const uint32_t hi = order[d];
-        t.list_of(hi, &ids);
-        DevNode& dn = out->nodes[d];
-        dn.tri_first = (uint32_t)out->tris.size();
-        dn.tri_n = (uint32_t)ids.size();
-        out->n_stored += ids.size();
-        if (hi == 0) out->root_list = ids.size();
-        else out->max_list = std::max<uint64_t>(out->max_list, ids.size());
-        for (int k = 0; k < 3; ++k) { dn.list_box[k] = -INFINITY; dn.list_box[3 + k] = INFINITY; }
+    // triangle records and culling hierarchies, node by node.  Lists are independent: every list builds
+    // its hierarchy into its own vector (indices local to the list) on an OpenMP thread, then the pieces are
+    // concatenated in node order, which makes the result independent of the thread count.
+    const size_t n_dev = order.size();
+    std::vector<uint64_t> tri_off(n_dev + 1, 0);
+    for (size_t d = 0; d < n_dev; ++d) tri_off[d + 1] = tri_off[d] + t.nodes[order[d]].list_len;
+    out->n_stored = tri_off[n_dev];
+    out->tris.resize(tri_off[n_dev]);
+    std::vector<std::vector<DevCull>> pieces(n_dev);
+    const uint32_t leaf_short = cull_threshold ? std::min(cull_threshold, 8u) : 8u;
+    const bool tight = cull_threshold != 0;
+    const uint32_t leaf_max = tight ? std::max(1u, std::min(cull_leaf, 8u)) : 8u;
+#pragma omp parallel
+    {
+        std::vector<uint32_t> ids;
+#pragma omp for schedule(dynamic, 64)
+        for (long long dd = 0; dd < (long long)n_dev; ++dd) {
+            const size_t d = (size_t)dd;
+            t.list_of(order[d], &ids);
+            DevNode& dn = out->nodes[d];
+            dn.tri_first = (uint32_t)tri_off[d];
+            dn.tri_n = (uint32_t)ids.size();
+            for (int k = 0; k < 3; ++k) { dn.list_box[k] = -INFINITY; dn.list_box[3 + k] = INFINITY; }
 #if RRT_CULL_F32
-        if (!ids.empty() && cull_threshold != 0 && out->scale < INFINITY) {
-            double b[6], tb[6];
-            for (int k = 0; k < 3; ++k) { b[k] = INFINITY; b[3 + k] = -INFINITY; }
-            for (uint32_t id : ids) {
-                tri_box(v + 9 * (size_t)id, tb);
-                for (int k = 0; k < 3; ++k) { b[k] = std::fmin(b[k], tb[k]); b[3 + k] = std::fmax(b[3 + k], tb[3 + k]); }
+            if (!ids.empty() && tight && out->scale < INFINITY) {
+                double b[6], tb[6];
+                for (int k = 0; k < 3; ++k) { b[k] = INFINITY; b[3 + k] = -INFINITY; }
+                for (uint32_t id : ids) {
+                    tri_box(v + 9 * (size_t)id, tb);
+                    for (int k = 0; k < 3; ++k) { b[k] = std::fmin(b[k], tb[k]); b[3 + k] = std::fmax(b[3 + k], tb[3 + k]); }
+                }
+                const double pad = kCullPadRel * out->scale;
+                for (int k = 0; k < 3; ++k) {
+                    dn.list_box[k] = CullBuilder::down(b[k] - pad);
+                    dn.list_box[3 + k] = CullBuilder::up(b[3 + k] + pad);
+                }
             }
-            const double pad = kCullPadRel * out->scale;
-            for (int k = 0; k < 3; ++k) {
-                dn.list_box[k] = CullBuilder::down(b[k] - pad);
-                dn.list_box[3 + k] = CullBuilder::up(b[3 + k] + pad);
-            }
-        }
 #endif
-        if (ids.empty()) {
-            dn.cull_root = UINT32_MAX;
-        } else if (ids.size() <= (cull_threshold ? std::min(cull_threshold, 8u) : 8u)) {
-            dn.cull_root = CullBuilder::leaf_word(dn.tri_first, (uint32_t)ids.size());  // short list: one leaf
-        } else {
-            const bool tight = cull_threshold != 0;
-            std::vector<double> boxes(6 * ids.size());
-            for (size_t i = 0; i < ids.size(); ++i) tri_box(v + 9 * (size_t)ids[i], &boxes[6 * i]);
-            CullBuilder cb{v, ids, std::move(boxes), out->cull, dn.tri_first, tight, tight ? std::max(1u, std::min(cull_leaf, 8u)) : 8u, out->scale};
-            dn.cull_root = cb.build(0, (uint32_t)ids.size());
-        }
-        for (uint32_t id : ids) {
-            const double* p = v + 9 * (size_t)id;
-            DevTri r{};
-            for (int k = 0; k < 3; ++k) {
-                r.v1[k] = p[k];
-                r.e1[k] = p[3 + k] - p[k];  // ray.rs:60
-                r.e2[k] = p[6 + k] - p[k];  // ray.rs:61
+            if (ids.empty()) {
+                dn.cull_root = UINT32_MAX;
+            } else if (ids.size() <= leaf_short) {
+                dn.cull_root = CullBuilder::leaf_word(dn.tri_first, (uint32_t)ids.size());  // short list: one leaf
+            } else {
+                std::vector<double> boxes(6 * ids.size());
+                for (size_t i = 0; i < ids.size(); ++i) tri_box(v + 9 * (size_t)ids[i], &boxes[6 * i]);
+                CullBuilder cb{v, ids, std::move(boxes), pieces[d], dn.tri_first, tight, leaf_max, out->scale};
+                dn.cull_root = cb.build(0, (uint32_t)ids.size());   // index local to pieces[d]; rebased below
             }
-            r.id = id;
-            out->tris.push_back(r);
+            DevTri* rec = out->tris.data() + tri_off[d];
+            for (uint32_t id : ids) {
+                const double* p = v + 9 * (size_t)id;
+                DevTri r{};
+                for (int k = 0; k < 3; ++k) {
+                    r.v1[k] = p[k];
+                    r.e1[k] = p[3 + k] - p[k];  // ray.rs:60
+                    r.e2[k] = p[6 + k] - p[k];  // ray.rs:61
+                }
+                r.id = id;
+                *rec++ = r;
+            }
         }
+    }
+    for (size_t d = 0; d < n_dev; ++d) {
+        const uint64_t len = t.nodes[order[d]].list_len;
+        if (order[d] == 0) out->root_list = len;
+        else out->max_list = std::max<uint64_t>(out->max_list, len);
+    }
+    // concatenate the hierarchies; inner-node references (bit31 clear) move by the piece's base
+    size_t n_cull = 0;
+    for (const auto& pc : pieces) n_cull += pc.size();
+    out->cull.reserve(n_cull);
+    for (size_t d = 0; d < n_dev; ++d) {
+        std::vector<DevCull>& pc = pieces[d];
+        if (pc.empty()) continue;
+        const uint32_t base = (uint32_t)out->cull.size();
+        out->nodes[d].cull_root += base;   // a list with a hierarchy has an inner node as its root
+        for (DevCull& c : pc) {
+            for (int k = 0; k < 2; ++k)
+                if (!(c.child[k] & 0x80000000u)) c.child[k] += base;
+            out->cull.push_back(c);
+        }
+        std::vector<DevCull>().swap(pc);
     }
 }
 

@@ -2,6 +2,7 @@
 the reference's incremental construction (src/collision/octree.rs:41-241) node for node — the tree
 shape decides tie winners and reachability.  Checked against the oracle's Vec-of-Vec restatement."""
 import ctypes as C
+import os
 
 import numpy as np
 import pytest
@@ -76,3 +77,30 @@ def test_depth_limit_is_an_error_not_a_crash(rrt):
     rmin, rmax = (C.c_double * 3)(*sd.root_min), (C.c_double * 3)(*sd.root_max)
     rc = L.rrt_octree_build(sd.v.ctypes.data, sd.n_tris, rmin, rmax, C.byref(h))
     assert rc == -5 and b"deeper" in L.rrt_last_error()
+
+
+def test_flatten_is_independent_of_thread_count(rrt):
+    # the per-list culling hierarchies are built on OpenMP threads and concatenated in node order:
+    # the flattened arrays (digest over nodes, records, culling nodes) must not depend on the thread count
+    import subprocess
+    import sys
+    code = (
+        "import ctypes as C, sys\n"
+        "sys.path.insert(0, %r)\n"
+        "import rrt_b200\n"
+        "from rrt_b200 import abi\n"
+        "from rrt_b200.synthetic import triangle_soup\n"
+        "sd = triangle_soup(60000, size=0.5)\n"
+        "L = abi.lib(); h = C.c_void_p()\n"
+        "lo = (C.c_double * 3)(-20, -20, -20); hi = (C.c_double * 3)(20, 20, 20)\n"
+        "abi.check(L.rrt_octree_build(sd.v.ctypes.data, sd.n_tris, lo, hi, C.byref(h)))\n"
+        "st = abi.SceneStats(); sec = C.c_double()\n"
+        "abi.check(L.rrt_octree_flatten_stats(h, sd.v.ctypes.data, C.byref(st), C.byref(sec)))\n"
+        "print(st.flat_digest, st.n_cull_nodes, st.n_tris_stored)\n"
+    ) % os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    outs = []
+    for threads in ("1", "5"):
+        r = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, OMP_NUM_THREADS=threads),
+                           capture_output=True, text=True, check=True)
+        outs.append(r.stdout.strip())
+    assert outs[0] == outs[1] and int(outs[0].split()[2]) == 60000
