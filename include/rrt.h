@@ -219,6 +219,10 @@ int rrt_octree_build(const double* v /* n x 9 */, uint64_t n_tris,
                      const double root_min[3], const double root_max[3], rrt_octree** out);
 void rrt_octree_destroy(rrt_octree* t);
 uint64_t rrt_octree_node_count(const rrt_octree* t);
+/* FNV-1a over every node (box, first child, triangle_count, list ends, depth) and the list links: two trees
+ * are the same tree iff the digests agree (used to check the parallel builder against sequential insertion;
+ * RRT_OCTREE_BUILD=seq|par selects the builder, default par from 20 000 triangles). */
+uint64_t rrt_octree_digest(const rrt_octree* t);
 /* For node i: box (6 doubles min.xyz max.xyz), triangle_count (octree.rs:11), first child index
  * (0 = leaf; children are 8 consecutive nodes, octree.rs:226-237), list length. */
 int rrt_octree_node(const rrt_octree* t, uint64_t i, double box[6], uint64_t* triangle_count,

@@ -81,7 +81,7 @@ SYMBOLS = [
     "rrt_ipc_close_handle", "rrt_copy_frame_to_host",
     "rrt_trace_rays", "rrt_ray_colours", "rrt_render_counters",
     "rrt_octree_build", "rrt_octree_destroy", "rrt_octree_node_count", "rrt_octree_node", "rrt_octree_node_list",
-    "rrt_octree_flatten_stats",
+    "rrt_octree_flatten_stats", "rrt_octree_digest",
     "rrt_obj_load", "rrt_obj_destroy", "rrt_obj_n_tris", "rrt_obj_v", "rrt_obj_vt", "rrt_obj_vn",
     "rrt_obj_material_id", "rrt_obj_n_materials", "rrt_obj_materials", "rrt_obj_material_name",
     "rrt_obj_n_textures", "rrt_obj_texture_name", "rrt_write_ppm", "rrt_microbench_fp64", "rrt_selftest_division",
@@ -129,6 +129,8 @@ def lib():
     L.rrt_octree_node_count.argtypes = [vp]
     L.rrt_octree_node_count.restype = u64
     L.rrt_octree_node.argtypes = [vp, u64, dp, C.POINTER(u64), C.POINTER(u64), C.POINTER(u64)]
+    L.rrt_octree_digest.argtypes = [vp]
+    L.rrt_octree_digest.restype = u64
     L.rrt_octree_flatten_stats.argtypes = [vp, vp, C.POINTER(SceneStats), dp]
     L.rrt_octree_node_list.argtypes = [vp, u64, vp, u64]
     L.rrt_octree_node_list.restype = C.c_int64

@@ -39,6 +39,13 @@ uint32_t cull_threshold() {
     if (s && *s) return (uint32_t)std::strtoul(s, nullptr, 10);
     return 1;
 }
+// RRT_OCTREE_BUILD=seq forces the sequential insertion loop (the literal octree.rs algorithm); default: the
+// order-exact parallel construction for anything big enough to matter.
+bool build_tree(HostOctree& tree, const double* v, uint64_t n, const double* lo, const double* hi, std::string* err) {
+    const char* s = std::getenv("RRT_OCTREE_BUILD");
+    const bool seq = s ? std::string(s) == "seq" : n < 20000;
+    return seq ? tree.build(v, n, lo, hi, err) : tree.build_parallel(v, n, lo, hi, err);
+}
 uint32_t cull_leaf() {
     const char* s = std::getenv("RRT_CULL_LEAF");
     if (s && *s) return (uint32_t)std::strtoul(s, nullptr, 10);
@@ -192,7 +199,7 @@ int rrt_scene_create(const rrt_scene_desc* d, int device, rrt_scene** out) {
     // host: exact reference octree, then flatten
     HostOctree tree;
     std::string err;
-    if (!tree.build(d->v, d->n_tris, d->root_min, d->root_max, &err)) return fail(RRT_ERR_DEPTH, err);
+    if (!build_tree(tree, d->v, d->n_tris, d->root_min, d->root_max, &err)) return fail(RRT_ERR_DEPTH, err);
     FlatScene flat;
     flatten(tree, d->v, cull_threshold(), cull_leaf(), &flat);
 
@@ -226,7 +233,8 @@ int rrt_scene_create(const rrt_scene_desc* d, int device, rrt_scene** out) {
     // shading records by original triangle id (entities.rs:78-84)
     {
         std::vector<DevShade> sh(d->n_tris);
-        for (uint64_t i = 0; i < d->n_tris; ++i) {
+#pragma omp parallel for schedule(static)
+        for (long long i = 0; i < (long long)d->n_tris; ++i) {
             const double *n = d->vn + 9 * i, *t = d->vt + 6 * i;
             DevShade& s = sh[i];
             std::memcpy(s.n1, n, 24); std::memcpy(s.n2, n + 3, 24); std::memcpy(s.n3, n + 6, 24);
@@ -477,12 +485,13 @@ int rrt_octree_build(const double* v, uint64_t n_tris, const double root_min[3],
     if (n_tris > 0x7FFFFFF0ull) return fail(RRT_ERR_INVALID, "too many triangles");
     auto t = std::make_unique<rrt_octree>();
     std::string err;
-    if (!t->t.build(v, n_tris, root_min, root_max, &err)) return fail(RRT_ERR_DEPTH, err);
+    if (!build_tree(t->t, v, n_tris, root_min, root_max, &err)) return fail(RRT_ERR_DEPTH, err);
     *out = t.release();
     return RRT_OK;
 }
 void rrt_octree_destroy(rrt_octree* t) { delete t; }
 uint64_t rrt_octree_node_count(const rrt_octree* t) { return t ? t->t.nodes.size() : 0; }
+uint64_t rrt_octree_digest(const rrt_octree* t) { return t ? t->t.digest() : 0; }
 int rrt_octree_node(const rrt_octree* t, uint64_t i, double box[6], uint64_t* triangle_count, uint64_t* first_child,
                     uint64_t* list_len) {
     if (!t || i >= t->t.nodes.size()) return fail(RRT_ERR_INVALID, "node index out of range");

@@ -5,9 +5,14 @@
 #include "rrt_octree.h"
 
 #include <algorithm>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <cmath>
 #include <cstring>
 #include <numeric>
+
+#include <omp.h>
 
 namespace rrt {
 
@@ -120,6 +125,197 @@ bool HostOctree::build(const double* v, uint64_t n, const double root_min[3], co
         }
     }
     return true;
+}
+
+// ---------------------------------------------------------------- parallel, order-exact construction
+namespace {
+
+struct TNode {
+    double box[6];
+    uint32_t depth = 0, count = 0, trigger = 0, first_child = 0;
+    std::vector<uint32_t> list;   // own list, insertion order
+    TNode* kids = nullptr;        // 8 children (octree.rs:216-225 order) once subdivided
+};
+
+struct ParBuild {
+    const double* v;
+    std::vector<std::vector<TNode*>> events;   // subdivided nodes, one bucket per OpenMP thread
+    bool too_deep = false;
+
+    // seq = the triangles that reach this node, in insertion order (all overlap its box)
+    void run(TNode* nd, std::vector<uint32_t>& seq) {
+        nd->count = (uint32_t)seq.size();  // octree.rs:75, once per arriving triangle
+        if (seq.empty()) return;
+        nd->list.push_back(seq[0]);  // octree.rs:77-78: the first triangle of an empty leaf stays for ever
+        if (seq.size() == 1) return;
+        if (nd->depth + 1 > (uint32_t)kMaxOctreeDepth) {
+#pragma omp atomic write
+            too_deep = true;
+            return;
+        }
+        nd->trigger = seq[1];  // octree.rs:79-80: the second arrival subdivides
+        nd->kids = new TNode[8];
+        events[(size_t)omp_get_thread_num()].push_back(nd);
+        const double x0 = nd->box[0], y0 = nd->box[1], z0 = nd->box[2], x1 = nd->box[3], y1 = nd->box[4], z1 = nd->box[5];
+        const double xm = x0 + (x1 - x0) / 2.0, ym = y0 + (y1 - y0) / 2.0, zm = z0 + (z1 - z0) / 2.0;  // octree.rs:136-146
+        for (int k = 0; k < 8; ++k) {
+            const bool xh = (k == 2 || k == 3 || k == 6 || k == 7), yh = k >= 4, zh = (k == 1 || k == 2 || k == 5 || k == 6);
+            TNode& c = nd->kids[k];
+            c.box[0] = xh ? xm : x0; c.box[3] = xh ? x1 : xm;
+            c.box[1] = yh ? ym : y0; c.box[4] = yh ? y1 : ym;
+            c.box[2] = zh ? zm : z0; c.box[5] = zh ? z1 : zm;
+            c.depth = nd->depth + 1;
+        }
+        std::vector<uint32_t> sub[8];
+        // octree.rs:82-104 for every later arrival: the routing of a triangle depends on its own box only, so a
+        // long sequence is classified in parallel (code 0..7 = the one child it overlaps, 8 = it stays here) and
+        // then distributed in order.
+        const size_t m = seq.size();
+        auto classify = [&](size_t i) -> uint8_t {
+            double tb[6];
+            tri_box(v + 9 * (size_t)seq[i], tb);
+            int hits = 0, only = 0;
+            for (int k = 0; k < 8; ++k)
+                if (boxes_overlap(nd->kids[k].box, tb)) { hits++; only = k; }
+            return (uint8_t)(hits == 1 ? only : 8);
+        };
+        if (m > 200000) {
+            std::vector<uint8_t> code(m);
+            uint8_t* cp = code.data();
+#pragma omp taskloop grainsize(32768) shared(cp)
+            for (long long i = 1; i < (long long)m; ++i) cp[i] = classify((size_t)i);
+            size_t cnt[9] = {0};
+            for (size_t i = 1; i < m; ++i) cnt[code[i]]++;
+            for (int k = 0; k < 8; ++k) sub[k].reserve(cnt[k]);
+            nd->list.reserve(1 + cnt[8]);
+            for (size_t i = 1; i < m; ++i) {
+                if (code[i] < 8) sub[code[i]].push_back(seq[i]);
+                else nd->list.push_back(seq[i]);
+            }
+        } else {
+            for (size_t i = 1; i < m; ++i) {
+                const uint8_t c = classify(i);
+                if (c < 8) sub[c].push_back(seq[i]);
+                else nd->list.push_back(seq[i]);
+            }
+        }
+        std::vector<uint32_t>().swap(seq);
+        for (int k = 0; k < 8; ++k) {
+            if (sub[k].size() > 2048) {
+                TNode* c = &nd->kids[k];
+                std::vector<uint32_t>* sq = new std::vector<uint32_t>(std::move(sub[k]));
+#pragma omp task firstprivate(c, sq)
+                {
+                    run(c, *sq);
+                    delete sq;
+                }
+            } else {
+                run(&nd->kids[k], sub[k]);
+            }
+        }
+    }
+};
+
+void free_tree(TNode* kids) {
+    if (!kids) return;
+    for (int k = 0; k < 8; ++k) free_tree(kids[k].kids);
+    delete[] kids;
+}
+
+}  // namespace
+
+bool HostOctree::build_parallel(const double* v, uint64_t n, const double root_min[3], const double root_max[3],
+                                std::string* err) {
+    nodes.clear();
+    next.assign(n, UINT32_MAX);
+    n_tris = n;
+    n_dropped = 0;
+    max_depth = 0;
+    TNode root;
+    for (int k = 0; k < 3; ++k) { root.box[k] = root_min[k]; root.box[3 + k] = root_max[k]; }
+    std::vector<uint32_t> seq;
+    {   // octree.rs:65,71-73: a triangle whose box misses the root box is dropped
+        std::vector<uint8_t> keep(n);
+#pragma omp parallel for schedule(static)
+        for (long long i = 0; i < (long long)n; ++i) {
+            double tb[6];
+            tri_box(v + 9 * (size_t)i, tb);
+            keep[(size_t)i] = boxes_overlap(tb, root.box) ? 1 : 0;
+        }
+        seq.reserve(n);
+        for (uint64_t i = 0; i < n; ++i) {
+            if (keep[i]) seq.push_back((uint32_t)i);
+            else n_dropped++;
+        }
+    }
+    const bool verbose = std::getenv("RRT_VERBOSE") != nullptr;
+    auto now = [] { return std::chrono::steady_clock::now(); };
+    auto secs = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
+        return std::chrono::duration<double>(b - a).count();
+    };
+    const auto t0 = now();
+    ParBuild pb{v};
+    pb.events.resize((size_t)omp_get_max_threads());
+#pragma omp parallel
+#pragma omp single
+    pb.run(&root, seq);
+    const auto t1 = now();
+    if (pb.too_deep) {
+        free_tree(root.kids);
+        if (err) *err = "octree deeper than kMaxOctreeDepth (coincident triangles?)";
+        return false;
+    }
+    // subdivision events in the order the sequential build performs them = by triggering triangle
+    std::vector<TNode*> ev;
+    for (auto& b : pb.events) ev.insert(ev.end(), b.begin(), b.end());
+    std::sort(ev.begin(), ev.end(), [](const TNode* a, const TNode* b) { return a->trigger < b->trigger; });
+    for (size_t r = 0; r < ev.size(); ++r) ev[r]->first_child = (uint32_t)(1 + 8 * r);
+    nodes.resize(1 + 8 * ev.size());
+    auto emit = [&](const TNode& t, uint32_t idx) {
+        HostNode h;
+        std::memcpy(h.box, t.box, sizeof h.box);
+        h.first_child = t.first_child;
+        h.triangle_count = t.count;
+        h.depth = t.depth;
+        h.list_len = (uint32_t)t.list.size();
+        if (!t.list.empty()) {
+            h.head = t.list.front();
+            h.tail = t.list.back();
+            for (size_t j = 0; j + 1 < t.list.size(); ++j) next[t.list[j]] = t.list[j + 1];
+        }
+        nodes[idx] = h;
+    };
+    emit(root, 0);
+    uint32_t md = 0;
+#pragma omp parallel for schedule(static) reduction(max : md)
+    for (long long r = 0; r < (long long)ev.size(); ++r) {
+        for (int k = 0; k < 8; ++k) emit(ev[r]->kids[k], ev[r]->first_child + k);
+        md = std::max(md, ev[r]->depth + 1);
+    }
+    max_depth = md;
+    const auto t2 = now();
+    free_tree(root.kids);
+    if (verbose)
+        std::fprintf(stderr, "[rrt] build_parallel: partition %.2fs, number+emit %.2fs, free %.2fs\n", secs(t0, t1), secs(t1, t2),
+                     secs(t2, now()));
+    return true;
+}
+
+uint64_t HostOctree::digest() const {
+    uint64_t h = 1469598103934665603ull;
+    auto mix = [&h](const void* p, size_t n) {
+        const unsigned char* b = static_cast<const unsigned char*>(p);
+        for (size_t i = 0; i < n; ++i) { h ^= b[i]; h *= 1099511628211ull; }
+    };
+    for (const HostNode& n : nodes) {
+        mix(n.box, sizeof n.box);
+        const uint32_t w[6] = {n.first_child, n.triangle_count, n.head, n.tail, n.list_len, n.depth};
+        mix(w, sizeof w);
+    }
+    mix(next.data(), next.size() * sizeof(uint32_t));
+    const uint64_t t[3] = {n_tris, n_dropped, max_depth};
+    mix(t, sizeof t);
+    return h;
 }
 
 void HostOctree::list_of(uint32_t node, std::vector<uint32_t>* out) const {

@@ -31,6 +31,14 @@ struct HostOctree {
     // Sequential insertion, bit-identical to Octree::push_triangle for i = 0..n-1 (octree.rs:41-108).
     // v = n x 9 doubles. Returns false (err set) if the tree exceeds kMaxOctreeDepth.
     bool build(const double* v, uint64_t n, const double root_min[3], const double root_max[3], std::string* err);
+    // The same tree — same boxes, lists, counts AND node numbering — built top-down on OpenMP tasks.
+    // Why it is the same tree: once a node is subdivided, a triangle is routed by its own box alone (into
+    // the one child it overlaps, or it stays), so the subsequence of triangles entering a child evolves
+    // independently of its siblings; a leaf keeps its first triangle and is subdivided by its second
+    // (octree.rs:77-80), which then lands in a fresh empty child or stays — so every subdivision has ONE
+    // triggering triangle, and the sequential build appends the 8 children in order of that triangle's index.
+    bool build_parallel(const double* v, uint64_t n, const double root_min[3], const double root_max[3], std::string* err);
+    uint64_t digest() const;   // FNV-1a over nodes and list links (tests: sequential == parallel)
     void list_of(uint32_t node, std::vector<uint32_t>* out) const;
 };
 

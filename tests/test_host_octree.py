@@ -104,3 +104,37 @@ def test_flatten_is_independent_of_thread_count(rrt):
                            capture_output=True, text=True, check=True)
         outs.append(r.stdout.strip())
     assert outs[0] == outs[1] and int(outs[0].split()[2]) == 60000
+
+
+def _tree_digest(rrt, sd):
+    L = rrt.abi.lib()
+    h = C.c_void_p()
+    rmin, rmax = (C.c_double * 3)(*sd.root_min), (C.c_double * 3)(*sd.root_max)
+    rrt.abi.check(L.rrt_octree_build(sd.v.ctypes.data, sd.n_tris, rmin, rmax, C.byref(h)))
+    out = (L.rrt_octree_digest(h), L.rrt_octree_node_count(h))
+    L.rrt_octree_destroy(h)
+    return out
+
+
+def test_parallel_builder_is_the_sequential_tree(rrt, scenes, monkeypatch):
+    # the top-down OpenMP construction must give the tree of sequential insertion: boxes, lists, counts AND the
+    # node numbering (digest over every node and list link).  Cases: shipped scenes, soups with many straddlers,
+    # coincident triangles (one subdivision per duplicate: a deep chain), triangles outside the root box.
+    from rrt_b200.synthetic import triangle_soup, sphere_grid
+    cases = [scenes("model"), scenes("model2"), scenes("model3"), triangle_soup(50000, size=0.6),
+             triangle_soup(300000, size=0.05), sphere_grid(nx=2, ny=2, nlon=64, nlat=32)]
+    dup = triangle_soup(3000, size=0.3)
+    dup.v[100:140] = dup.v[100]
+    far = triangle_soup(5000, extent=30.0, size=0.5)          # some boxes miss the +-20 root box: dropped
+    cases += [dup, far]
+    for sd in cases:
+        monkeypatch.setenv("RRT_OCTREE_BUILD", "seq")
+        a = _tree_digest(rrt, sd)
+        monkeypatch.setenv("RRT_OCTREE_BUILD", "par")
+        b = _tree_digest(rrt, sd)
+        assert a == b and a[1] >= 1
+
+
+def test_parallel_builder_node_for_node_against_oracle(rrt, monkeypatch):
+    monkeypatch.setenv("RRT_OCTREE_BUILD", "par")
+    assert_same_tree(rrt, random_scene(2500, seed=11))
