@@ -221,6 +221,7 @@ int rrt_scene_create(const rrt_scene_desc* d, int device, rrt_scene** out) {
     if ((rc = sc->upload(flat.nodes.data(), flat.nodes.size(), &sc->dev.nodes))) return rc;
     if ((rc = sc->upload(flat.tris.data(), flat.tris.size(), &sc->dev.tris))) return rc;
     if ((rc = sc->upload(flat.cull.data(), flat.cull.size(), &sc->dev.cull))) return rc;
+    if ((rc = sc->upload(flat.sub_boxes.data(), flat.sub_boxes.size(), &sc->dev.sub_boxes))) return rc;
     sc->dev.n_nodes = (uint32_t)flat.nodes.size();
     sc->dev.root_tri_count = st.n_tris_stored ? 1u : 0u;
     sc->dev.planes_safe = (flat.planes_safe && !std::getenv("RRT_SLOW_DIV")) ? 1u : 0u;
@@ -528,6 +529,7 @@ int rrt_octree_flatten_stats(const rrt_octree* t, const double* v, rrt_scene_sta
     mix(flat.nodes.data(), flat.nodes.size() * sizeof(DevNode));
     mix(flat.tris.data(), flat.tris.size() * sizeof(DevTri));
     mix(flat.cull.data(), flat.cull.size() * sizeof(DevCull));
+    mix(flat.sub_boxes.data(), flat.sub_boxes.size() * sizeof(DevSubBox));
     out->flat_digest = h;
     return RRT_OK;
 }

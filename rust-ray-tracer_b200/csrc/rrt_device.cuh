@@ -28,6 +28,7 @@ struct DevScene {
     const DevNode* nodes;
     const DevTri* tris;
     const DevCull* cull;
+    const DevSubBox* sub_boxes;
     const DevShade* shade;
     const DevMaterial* materials;
     const DevTexture* tex;

@@ -554,6 +554,7 @@ void flatten(const HostOctree& t, const double* v, uint32_t cull_threshold, uint
     out->n_stored = tri_off[n_dev];
     out->tris.resize(tri_off[n_dev]);
     std::vector<std::vector<DevCull>> pieces(n_dev);
+    std::vector<double> own_box(6 * n_dev);   // unpadded f64 box of every own list (empty: +inf/-inf)
     const uint32_t leaf_short = cull_threshold ? std::min(cull_threshold, 8u) : 8u;
     const bool tight = cull_threshold != 0;
     const uint32_t leaf_max = tight ? std::max(1u, std::min(cull_leaf, 8u)) : 8u;
@@ -568,14 +569,19 @@ void flatten(const HostOctree& t, const double* v, uint32_t cull_threshold, uint
             dn.tri_first = (uint32_t)tri_off[d];
             dn.tri_n = (uint32_t)ids.size();
             for (int k = 0; k < 3; ++k) { dn.list_box[k] = -INFINITY; dn.list_box[3 + k] = INFINITY; }
-#if RRT_CULL_F32
-            if (!ids.empty() && tight && out->scale < INFINITY) {
-                double b[6], tb[6];
-                for (int k = 0; k < 3; ++k) { b[k] = INFINITY; b[3 + k] = -INFINITY; }
+            {
+                double* ob = &own_box[6 * d];
+                double tb[6];
+                for (int k = 0; k < 3; ++k) { ob[k] = INFINITY; ob[3 + k] = -INFINITY; }
                 for (uint32_t id : ids) {
                     tri_box(v + 9 * (size_t)id, tb);
-                    for (int k = 0; k < 3; ++k) { b[k] = std::fmin(b[k], tb[k]); b[3 + k] = std::fmax(b[3 + k], tb[3 + k]); }
+                    for (int k = 0; k < 3; ++k) { ob[k] = std::fmin(ob[k], tb[k]); ob[3 + k] = std::fmax(ob[3 + k], tb[3 + k]); }
                 }
+            }
+#if RRT_CULL_F32
+            if (!ids.empty() && tight && out->scale < INFINITY) {
+                double b[6];
+                std::memcpy(b, &own_box[6 * d], sizeof b);
                 const double pad = kCullPadRel * out->scale;
                 for (int k = 0; k < 3; ++k) {
                     dn.list_box[k] = CullBuilder::down(b[k] - pad);
@@ -611,6 +617,28 @@ void flatten(const HostOctree& t, const double* v, uint32_t cull_threshold, uint
         const uint64_t len = t.nodes[order[d]].list_len;
         if (order[d] == 0) out->root_list = len;
         else out->max_list = std::max<uint64_t>(out->max_list, len);
+    }
+    // subtree boxes, bottom-up: kept children have larger device indices than their parent (breadth-first order)
+    out->sub_boxes.assign(n_dev, DevSubBox{});
+    for (size_t d = n_dev; d-- > 0;) {
+        double* b = &own_box[6 * d];
+        const DevNode& dn = out->nodes[d];
+        const uint32_t nk = (uint32_t)__builtin_popcount(dn.child_mask);
+        for (uint32_t c = 0; c < nk; ++c) {
+            const double* cb = &own_box[6 * (size_t)(dn.first_child + c)];   // already the child's SUBTREE box
+            for (int k = 0; k < 3; ++k) { b[k] = std::fmin(b[k], cb[k]); b[3 + k] = std::fmax(b[3 + k], cb[3 + k]); }
+        }
+        DevSubBox& sb = out->sub_boxes[d];
+        for (int k = 0; k < 3; ++k) { sb.box[k] = -INFINITY; sb.box[3 + k] = INFINITY; }
+#if RRT_CULL_F32
+        if (tight && out->scale < INFINITY) {
+            const double pad = kCullPadRel * out->scale;
+            for (int k = 0; k < 3; ++k) {
+                sb.box[k] = CullBuilder::down(b[k] - pad);
+                sb.box[3 + k] = CullBuilder::up(b[3 + k] + pad);
+            }
+        }
+#endif
     }
     // concatenate the hierarchies; inner-node references (bit31 clear) move by the piece's base
     size_t n_cull = 0;

@@ -107,8 +107,18 @@ struct alignas(16) DevCull {
 static_assert(sizeof(DevCull) == 112, "DevCull layout");
 #endif
 
+// Conservative (padded, outward-rounded) f32 box of EVERYTHING below a node: its own list and the lists of all
+// its descendants.  A ray that misses it gets None from the whole subtree (ray.rs:104-168 can only return a
+// triangle the exact test accepts), so the node is skipped on entry.  32 bytes, parallel to nodes[].
+struct alignas(32) DevSubBox {
+    float box[6];
+    uint32_t _pad[2];
+};
+static_assert(sizeof(DevSubBox) == 32, "DevSubBox layout");
+
 struct FlatScene {
     std::vector<DevNode> nodes;
+    std::vector<DevSubBox> sub_boxes;
     std::vector<DevTri> tris;
     std::vector<DevCull> cull;
     uint64_t n_stored = 0, root_list = 0, max_list = 0;

@@ -182,6 +182,9 @@ __device__ __forceinline__ bool test_record(const V3& o, const V3& d, const DevT
     return false;
 }
 
+#ifndef RRT_SUB_BOX
+#define RRT_SUB_BOX 1
+#endif
 #ifndef RRT_LIST_BOX
 #define RRT_LIST_BOX 1
 #endif
@@ -220,6 +223,20 @@ __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const 
 #endif
 
     for (;;) {
+#if RRT_CULL_F32 && RRT_SUB_BOX
+        // everything below this node (own list + all descendants) lies inside sub_boxes[node]: a ray that
+        // misses it gets None from the whole subtree, exactly what walking it would return.
+        bool enter = true;
+        if (!is_root) {
+            const float4* sb = reinterpret_cast<const float4*>(sc.sub_boxes + node);
+            const float4 s0 = __ldg(sb);
+            const float2 s1 = __ldg(reinterpret_cast<const float2*>(sb + 1));
+            float tn;
+            if (COUNT) tc.cull++;
+            enter = cull_box(cr, s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, __int_as_float(0x7f800000), tn);
+        }
+        if (enter) {
+#endif
         const DevNode* __restrict__ n = sc.nodes + node;
         const uint4 m = __ldg(reinterpret_cast<const uint4*>(&n->first_child));  // first_child, child_mask, tri_first, tri_n
         if (COUNT) tc.nodes++;
@@ -391,6 +408,9 @@ __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const 
             }
         }
 
+#if RRT_CULL_F32 && RRT_SUB_BOX
+        }
+#endif
         // ---- next node: first remaining child of the deepest open level (ray.rs:152-161)
         if ((lv_ord >> 24) == 0u) {
             if (sp == 0) return;
