@@ -183,7 +183,7 @@ __device__ __forceinline__ bool test_record(const V3& o, const V3& d, const DevT
 }
 
 #ifndef RRT_SUB_BOX
-#define RRT_SUB_BOX 1
+#define RRT_SUB_BOX 2     // 1: test a node's subtree box on entry; 2: at the parent, for the children its exact slabs hit
 #endif
 #ifndef RRT_LIST_BOX
 #define RRT_LIST_BOX 1
@@ -223,7 +223,7 @@ __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const 
 #endif
 
     for (;;) {
-#if RRT_CULL_F32 && RRT_SUB_BOX
+#if RRT_CULL_F32 && RRT_SUB_BOX == 1
         // everything below this node (own list + all descendants) lies inside sub_boxes[node]: a ray that
         // misses it gets None from the whole subtree, exactly what walking it would return.
         bool enter = true;
@@ -382,6 +382,23 @@ __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const 
             }
             hitmask &= m.y;
             if (COUNT) tc.box += __popc(m.y);
+#if RRT_CULL_F32 && RRT_SUB_BOX == 2
+            // A child whose SUBTREE box (own list + all descendants, padded f32, DevSubBox) the ray misses
+            // returns None (ray.rs:104-168 can only return a triangle the exact test accepts); dropping it from
+            // the sorted list is invisible (stable sort; None children are skipped by the loop at ray.rs:152-161).
+            // Tested here, for the children the exact slabs hit, rather than on entry: no sort slot, no push/pop,
+            // and the box loads of one node are independent of each other.
+            for (uint32_t left = hitmask; left;) {
+                const uint32_t kk = (uint32_t)__ffs(left) - 1u;
+                left &= left - 1u;
+                const float4* sb = reinterpret_cast<const float4*>(sc.sub_boxes + (m.x + (uint32_t)__popc(m.y & ((1u << kk) - 1u))));
+                const float4 s0 = __ldg(sb);
+                const float2 s1 = __ldg(reinterpret_cast<const float2*>(sb + 1));
+                float tn;
+                if (COUNT) tc.cull++;
+                if (!cull_box(cr, s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, __int_as_float(0x7f800000), tn)) hitmask &= ~(1u << kk);
+            }
+#endif
             if (hitmask) {
                 // stable sort by key (ray.rs:146-147) as repeated selection of the smallest remaining key,
                 // lowest child index first among equals; the last remaining child needs no comparison.
@@ -408,7 +425,7 @@ __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const 
             }
         }
 
-#if RRT_CULL_F32 && RRT_SUB_BOX
+#if RRT_CULL_F32 && RRT_SUB_BOX == 1
         }
 #endif
         // ---- next node: first remaining child of the deepest open level (ray.rs:152-161)
