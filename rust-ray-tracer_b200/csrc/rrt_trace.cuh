@@ -151,7 +151,10 @@ __device__ __forceinline__ bool cull_box(const CullRay& c, float bx0, float by0,
     const float z0 = fmaf(bz0, c.iz, c.cz), z1 = fmaf(bz1, c.iz, c.cz);
     tnear = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fminf(z0, z1));
     const float tfar = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fmaxf(z0, z1));
-    return !c.ok || ((tnear <= tfar) && (tfar >= 0.0f) && (tnear <= limit));
+    // tnear <= tfar && tfar >= 0 && tnear <= limit, as ONE comparison.  The folded form additionally demands
+    // limit >= 0, which only ever fails for a caller-supplied max_t < 0 — and then nothing can be accepted anyway
+    // (every accepted t is > EPSILON); a NaN limit is ignored by fminf, i.e. it prunes nothing.
+    return !c.ok || (fmaxf(tnear, 0.0f) <= fminf(tfar, limit));
 }
 #endif
 
