@@ -185,6 +185,12 @@ __device__ __forceinline__ bool test_record(const V3& o, const V3& d, const DevT
     return false;
 }
 
+#ifndef RRT_SORT_NOUNROLL
+#define RRT_SORT_NOUNROLL 1
+#endif
+#ifndef RRT_LEAF_NOUNROLL
+#define RRT_LEAF_NOUNROLL 1
+#endif
 #ifndef RRT_SUB_BOX
 #define RRT_SUB_BOX 2     // 1: test a node's subtree box on entry; 2: at the parent, for the children its exact slabs hit
 #endif
@@ -329,6 +335,9 @@ __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const 
                     const uint32_t first = cur & 0x0FFFFFFFu;
                     const uint32_t cnt = ((cur >> 28) & 7u) + 1u;
                     bool upd = false;
+#if RRT_LEAF_NOUNROLL
+#pragma unroll 1
+#endif
                     for (uint32_t i = 0; i < cnt; ++i) {
                         if (COUNT) tc.mt++;
                         upd |= test_record(o, d, sc.tris, first + i, nb);
@@ -407,6 +416,9 @@ __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const 
                 // lowest child index first among equals; the last remaining child needs no comparison.
                 uint32_t order = 0, rem = hitmask, shift = 0;
                 const uint32_t nh = __popc(hitmask);
+#if RRT_SORT_NOUNROLL
+#pragma unroll 1
+#endif
                 for (uint32_t r = 1; r < nh; ++r) {
                     double bk = 0.0;
                     uint32_t bi = 8;
