@@ -49,10 +49,23 @@ struct V3 {
 __device__ __forceinline__ V3 operator+(V3 a, V3 b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
 __device__ __forceinline__ V3 operator-(V3 a, V3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
 __device__ __forceinline__ V3 operator*(V3 a, double s) { return {a.x * s, a.y * s, a.z * s}; }
-__device__ __forceinline__ V3 operator/(V3 a, double s) { return {a.x / s, a.y / s, a.z / s}; }
+// IEEE division / square root as CALLS (shading only: cold code, ~40 / ~25 inlined instructions per site
+// otherwise, and render_kernel is instruction-cache sensitive — profiles/r01_experiments.md).  Same
+// correctly rounded operations, same bits.
+#ifndef RRT_SHADE_CALLS
+#define RRT_SHADE_CALLS 1
+#endif
+#if RRT_SHADE_CALLS
+static __device__ __noinline__ double div_rn(double a, double b) { return a / b; }
+static __device__ __noinline__ double sqrt_rn(double a) { return sqrt(a); }
+#else
+__device__ __forceinline__ double div_rn(double a, double b) { return a / b; }
+__device__ __forceinline__ double sqrt_rn(double a) { return sqrt(a); }
+#endif
+__device__ __forceinline__ V3 operator/(V3 a, double s) { return {div_rn(a.x, s), div_rn(a.y, s), div_rn(a.z, s)}; }
 __device__ __forceinline__ V3 operator-(V3 a) { return {-a.x, -a.y, -a.z}; }
 __device__ __forceinline__ double dot(V3 a, V3 b) { return (a.x * b.x) + (a.y * b.y) + (a.z * b.z); }  // engine.rs:85-87
-__device__ __forceinline__ double length(V3 a) { return sqrt(a.x * a.x + a.y * a.y + a.z * a.z); }     // engine.rs:89-91
+__device__ __forceinline__ double length(V3 a) { return sqrt_rn(a.x * a.x + a.y * a.y + a.z * a.z); }  // engine.rs:89-91
 __device__ __forceinline__ V3 cross(V3 a, V3 b) {                                                       // engine.rs:93-99
     return {a.y * b.z - a.z * b.y, -(a.x * b.z - a.z * b.x), a.x * b.y - a.y * b.x};
 }
