@@ -58,10 +58,13 @@ __device__ __forceinline__ V3 operator*(V3 a, double s) { return {a.x * s, a.y *
 #if RRT_SHADE_CALLS
 static __device__ __noinline__ double div_rn(double a, double b) { return a / b; }
 static __device__ __noinline__ double sqrt_rn(double a) { return sqrt(a); }
+static __device__ __noinline__ double pow_call(double a, double b) { return pow(a, b); }
 #else
 __device__ __forceinline__ double div_rn(double a, double b) { return a / b; }
 __device__ __forceinline__ double sqrt_rn(double a) { return sqrt(a); }
+__device__ __forceinline__ double pow_call(double a, double b) { return pow(a, b); }
 #endif
+
 __device__ __forceinline__ V3 operator/(V3 a, double s) { return {div_rn(a.x, s), div_rn(a.y, s), div_rn(a.z, s)}; }
 __device__ __forceinline__ V3 operator-(V3 a) { return {-a.x, -a.y, -a.z}; }
 __device__ __forceinline__ double dot(V3 a, V3 b) { return (a.x * b.x) + (a.y * b.y) + (a.z * b.z); }  // engine.rs:85-87
@@ -119,7 +122,7 @@ __device__ __forceinline__ bool moller_trumbore(const V3& o, const V3& d, const 
     const double x = a < 0.0 ? -sh : sh;
     if (x > aa * 1.000000000001) return false;        // certainly u > 1
     if (x < -1e-200 && aa < 1e100) return false;      // certainly u < 0
-    const double f = 1.0 / a;                  // ray.rs:71
+    const double f = 1.0 / a;                  // ray.rs:71 (inline: a call here forces spills in the hot loop, c4 +15 %)
     u = f * sh;                                // ray.rs:73
     if (u < 0.0 || u > 1.0) return false;      // ray.rs:75
     const V3 q = cross(s, e1);                 // ray.rs:79

@@ -42,7 +42,7 @@ __device__ __forceinline__ void add_light(V3& I, const DevMaterial* __restrict__
         const double r_dot_v = dot(r, v);
         if (r_dot_v > 0.0) {
             const V3 ks{__ldg(&m->ks[0]), __ldg(&m->ks[1]), __ldg(&m->ks[2])};
-            I = I + ks * intensity * pow(div_rn(r_dot_v, length(r) * length(v)), s);  // raytracer.rs:293-295
+            I = I + ks * intensity * pow_call(div_rn(r_dot_v, length(r) * length(v)), s);  // raytracer.rs:293-295
             spec = true;
         }
     }
