@@ -155,6 +155,14 @@ void rrt_render_params_default(rrt_render_params* p);
 int rrt_scene_create(const rrt_scene_desc* desc, int device, rrt_scene** out);
 void rrt_scene_destroy(rrt_scene* scene);
 int rrt_scene_get_stats(const rrt_scene* scene, rrt_scene_stats* out);
+/* Dispatch-order hint (no counterpart in the reference: rayon steals rows dynamically, engine.rs:201-203).
+ * Every render call on a scene handle records what each 16x4-pixel block of the frame cost; the next call of the
+ * same shape (resolution and shard) hands the blocks out heaviest first, so the persistent kernel does not end on
+ * a slow tile.  Only the ORDER of the work changes: frames and hit ids are bit-identical with the hint on or off.
+ * enable = 1 (default; RRT_ORDER_HINT=0 in the environment turns it off at scene creation) | 0; either way the
+ * recorded order is dropped, so the next frame runs in raster order.  Render calls on ONE handle must be issued
+ * on one stream at a time (they share the handle's scratch and this state). */
+int rrt_scene_order_hint(rrt_scene* scene, int enable);
 
 /* ---- rendering (replaces Scene::draw_scene, engine.rs:186-255) ---- */
 /* Host-buffer call: fb_0rgb[width*height] receives the reference canvas layout

@@ -65,6 +65,7 @@ struct rrt_scene {
     uint32_t* d_scratch = nullptr;   // per-pixel accumulators + sample-queue head of the persistent kernel
     size_t fb_cap = 0, hit_cap = 0, scratch_cap = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    RenderSchedule sched;            // dispatch order of the next frame from the measured cost of this one (rrt_render.h)
 
     template <class T>
     int upload(const T* host, size_t n, const T** out) {
@@ -83,6 +84,7 @@ struct rrt_scene {
         if (d_fb) cudaFree(d_fb);
         if (d_hit) cudaFree(d_hit);
         if (d_scratch) cudaFree(d_scratch);
+        sched.release();
         if (ev0) cudaEventDestroy(ev0);
         if (ev1) cudaEventDestroy(ev1);
     }
@@ -205,6 +207,8 @@ int rrt_scene_create(const rrt_scene_desc* d, int device, rrt_scene** out) {
 
     auto sc = std::make_unique<rrt_scene>();
     sc->device = device;
+    if (const char* e = getenv("RRT_ORDER_HINT")) sc->sched.enabled = atoi(e) != 0;
+    if (const char* e = getenv("RRT_ORDER_TAIL")) sc->sched.tail_safety = (float)atof(e);   // tuning knob (rrt_render.h)
     rrt_scene_stats& st = sc->stats;
     st.n_tris = d->n_tris;
     st.n_tris_stored = flat.n_stored;
@@ -276,6 +280,14 @@ int rrt_scene_create(const rrt_scene_desc* d, int device, rrt_scene** out) {
 
 void rrt_scene_destroy(rrt_scene* s) { delete s; }
 
+int rrt_scene_order_hint(rrt_scene* s, int enable) {
+    if (!s) return fail(RRT_ERR_INVALID, "null scene");
+    s->sched.enabled = enable != 0;
+    s->sched.valid = false;
+    s->sched.n_blocks = 0;   // next launch re-arms the cost array
+    return RRT_OK;
+}
+
 int rrt_scene_get_stats(const rrt_scene* s, rrt_scene_stats* out) {
     if (!s || !out) return fail(RRT_ERR_INVALID, "null argument");
     *out = s->stats;
@@ -319,7 +331,7 @@ int rrt_render_device(rrt_scene* s, const rrt_render_params* p, const rrt_shard*
     if (rc) return rc;
     CU(cudaSetDevice(s->device));
     if ((rc = ensure(&s->d_scratch, &s->scratch_cap, render_scratch_words(P.n_rows_local, P.W)))) return rc;
-    CU(launch_render(s->dev, P, d_fb, d_hit_ids, s->d_scratch, nullptr, (cudaStream_t)cuda_stream));
+    CU(launch_render(s->dev, P, d_fb, d_hit_ids, s->d_scratch, nullptr, (cudaStream_t)cuda_stream, &s->sched));
     return RRT_OK;
 }
 
@@ -332,7 +344,7 @@ int rrt_render_device_into_frame(rrt_scene* s, const rrt_render_params* p, const
     P.full_frame = 1;
     CU(cudaSetDevice(s->device));
     if ((rc = ensure(&s->d_scratch, &s->scratch_cap, render_scratch_words(P.n_rows_local, P.W)))) return rc;
-    CU(launch_render(s->dev, P, d_frame, nullptr, s->d_scratch, nullptr, (cudaStream_t)cuda_stream));
+    CU(launch_render(s->dev, P, d_frame, nullptr, s->d_scratch, nullptr, (cudaStream_t)cuda_stream, &s->sched));
     return RRT_OK;
 }
 
@@ -392,7 +404,7 @@ int rrt_render(rrt_scene* s, const rrt_render_params* p, uint32_t* fb, int32_t* 
     if (hit_ids && (rc = ensure(&s->d_hit, &s->hit_cap, n * 4))) return rc;
     if ((rc = ensure(&s->d_scratch, &s->scratch_cap, render_scratch_words(P.n_rows_local, P.W)))) return rc;
     CU(cudaEventRecord(s->ev0, 0));
-    CU(launch_render(s->dev, P, s->d_fb, hit_ids ? s->d_hit : nullptr, s->d_scratch, nullptr, 0));
+    CU(launch_render(s->dev, P, s->d_fb, hit_ids ? s->d_hit : nullptr, s->d_scratch, nullptr, 0, &s->sched));
     CU(cudaEventRecord(s->ev1, 0));
     CU(cudaMemcpy(fb, s->d_fb, n * sizeof(uint32_t), cudaMemcpyDeviceToHost));
     if (hit_ids) CU(cudaMemcpy(hit_ids, s->d_hit, n * 4 * sizeof(int32_t), cudaMemcpyDeviceToHost));

@@ -3,6 +3,8 @@
 #include "rrt_render.h"
 #include "rrt_shade.cuh"
 
+#include <cub/device/device_radix_sort.cuh>
+
 namespace rrt {
 
 namespace {
@@ -21,6 +23,14 @@ constexpr int kBlock = RRT_BLOCK;
 constexpr int kTileW = 16;       // samples are enumerated in 16x4-pixel blocks of eight 4x2-pixel tiles,
 constexpr int kTileH = 4;        // 4 supersamples per pixel: 32 consecutive indices = one 8x4 half-pixel lattice
 
+#ifndef RRT_TIMELINE
+#define RRT_TIMELINE 0      // development aid (tools/drain_timeline.py): when does the queue run dry, when do warps exit
+#endif
+#if RRT_TIMELINE
+__device__ unsigned long long g_tl[4 + 256];   // [0] min start, [1] min queue-dry, [2] max exit, [3] warps; [4..] exits per 5 us after queue-dry
+__device__ __forceinline__ unsigned long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+#endif
+
 // compact row k of this shard -> buffer row (rrt_shard in rrt.h)
 __device__ __forceinline__ int buffer_row(const DevParams& P, int k) {
     if (P.n_shards <= 1) return k;
@@ -36,11 +46,12 @@ __device__ __forceinline__ int buffer_row(const DevParams& P, int k) {
 // The 4 samples of a pixel (engine.rs:207-236) may be finished by different lanes at different times:
 // each adds its colour into a packed per-pixel accumulator (10 bits per channel + 2-bit arrival count);
 // the 4th arrival divides by 4 (Color::mix, entities.rs:49-69) and stores the pixel (entities.rs:32-36).
-template <bool COUNT>
+template <bool COUNT, bool HINT>
 __global__ void __launch_bounds__(kBlock, RRT_MIN_BLOCKS)
 render_kernel(const DevScene sc, const __grid_constant__ DevParams P, uint32_t* __restrict__ fb,
               int32_t* __restrict__ hit_ids, uint32_t* __restrict__ acc, unsigned long long* __restrict__ next,
-              DevCounters* __restrict__ counters, const int tiles_x, const unsigned long long total) {
+              DevCounters* __restrict__ counters, const int tiles_x, const unsigned long long total,
+              const uint32_t* __restrict__ order, uint32_t* __restrict__ cost) {
     const unsigned lane = threadIdx.x & 31u;
     const unsigned lt_mask = (1u << lane) - 1u;
     __shared__ double park_s[RRT_PARK ? kParkWords * kBlock : 1];
@@ -51,22 +62,41 @@ render_kernel(const DevScene sc, const __grid_constant__ DevParams P, uint32_t* 
     unsigned k = 0;
     TraceCount tc_total;
     uint32_t n_primary = 0, n_shadow = 0, n_reflect = 0;
+    // dispatch-order hint (RenderSchedule): the 16x4-pixel block this warp is working on and when it fetched it
+    // (in shared memory: touched once per tile, and the hot loop has no register to spare)
+    __shared__ uint2 tile_info_s[HINT ? kBlock / 32 : 1];
+    uint2& tile_info = tile_info_s[HINT ? threadIdx.x >> 5 : 0];
+    if (HINT && lane == 0) tile_info = make_uint2(0xFFFFFFFFu, 0u);
+    __syncwarp();
+#if RRT_TIMELINE
+    if (lane == 0) atomicMin(&g_tl[0], gtime());
+#endif
 
     for (;;) {
         // ---- refill idle lanes from the global sample queue
         const unsigned idle = __ballot_sync(0xFFFFFFFFu, !active);
+        if (HINT && idle == 0xFFFFFFFFu && lane == 0 && tile_info.x != 0xFFFFFFFFu) {
+            // the warp is through with its tile: a block costs what its slowest tile took (SM cycles, fetch to last ray)
+            atomicMax(cost + tile_info.x, (uint32_t)clock() - tile_info.y);
+            tile_info.x = 0xFFFFFFFFu;
+        }
         if (__popc(idle) >= RRT_REFILL_MIN && !drained) {
             const int leader = __ffs(idle) - 1;
             unsigned long long base = 0;
             if ((int)lane == leader) base = atomicAdd(next, (unsigned long long)__popc(idle));
             base = __shfl_sync(0xFFFFFFFFu, base, leader);
             if (base + __popc(idle) >= total) drained = true;  // warp-uniform: the queue is (about to be) empty
+#if RRT_TIMELINE
+            if (drained && lane == 0) atomicMin(&g_tl[1], gtime());
+#endif
             if (!active) {
                 const unsigned long long s = base + __popc(idle & lt_mask);
                 if (s < total) {
                     const unsigned long long tile = s >> 5;
                     const unsigned l = (unsigned)s & 31u, p = l >> 2;
-                    const unsigned long long blk = tile >> 3;
+                    unsigned long long blk = tile >> 3;
+                    if (HINT && order) blk = __ldg(order + blk);   // the last part of the frame: heaviest blocks first
+                    if (HINT && lane == 0) tile_info = make_uint2((uint32_t)blk, (uint32_t)clock());   // one tile per fetch
                     const unsigned w = (unsigned)tile & 7u;
                     const int by = (int)(blk / (unsigned)tiles_x), bx = (int)(blk - (unsigned long long)by * tiles_x);
                     const int col = bx * kTileW + (int)(w & 3u) * 4 + (int)(p & 3u);
@@ -123,6 +153,16 @@ render_kernel(const DevScene sc, const __grid_constant__ DevParams P, uint32_t* 
             }
         }
     }
+#if RRT_TIMELINE
+    if (lane == 0) {
+        const unsigned long long t = gtime();
+        atomicMax(&g_tl[2], t);
+        atomicAdd(&g_tl[3], 1ull);
+        const unsigned long long q = g_tl[1];   // set before any warp can exit
+        unsigned long long b = t > q ? (t - q) / 5000ull : 0ull;
+        atomicAdd(&g_tl[4 + (b > 255ull ? 255ull : b)], 1ull);
+    }
+#endif
     if (COUNT) {
         n_shadow = st.rc.shadow; n_reflect = st.rc.reflect;
         unsigned long long v[7] = {n_primary, n_shadow, n_reflect, tc_total.mt, tc_total.box, tc_total.cull, tc_total.nodes};
@@ -182,11 +222,104 @@ __global__ void deinterleave_kernel(const uint32_t* __restrict__ g, int rows_per
     fb[i] = (r == 0) ? 0u : g[((size_t)s * rows_per_block + k) * W + c];
 }
 
+// RenderSchedule: {sum, max} of the block costs of the frame just rendered
+__global__ void order_stats_kernel(const uint32_t* __restrict__ cost, uint32_t n, unsigned long long* __restrict__ stats) {
+    unsigned long long sum = 0ull;
+    uint32_t mx = 0u;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint32_t c = cost[i];
+        sum += c;
+        mx = max(mx, c);
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        sum += __shfl_xor_sync(0xFFFFFFFFu, sum, o);
+        mx = max(mx, __shfl_xor_sync(0xFFFFFFFFu, mx, o));
+    }
+    if ((threadIdx.x & 31u) == 0u) {
+        atomicAdd(stats, sum);
+        atomicMax(stats + 1, (unsigned long long)mx);
+    }
+}
+
+// RenderSchedule: next frame's sort keys.  Blocks are handed out in raster order (good locality: the resident warps
+// work on a thin band of the frame) EXCEPT the last part of the sequence, which is sorted by descending cost class
+// (half octaves of the block's slowest tile) so that the kernel ends on its cheapest tiles.  How long that part must be
+// follows from this frame's own numbers: a tile fetched with less than (slowest tile) of the frame left can end up as
+// the tail; the frame lasts about (8 tiles per block x sum of block costs) / resident warps (an over-estimate: a block
+// costs its SLOWEST tile), so the last  safety x max / that  of the sequence is sorted (safety <= 0: all of it).
+__global__ void order_keys_kernel(uint32_t* __restrict__ cost, uint32_t* __restrict__ keys, uint32_t n,
+                                  const unsigned long long* __restrict__ stats, unsigned long long* __restrict__ stats_next,
+                                  float resident_warps, float safety) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) { stats_next[0] = 0ull; stats_next[1] = 0ull; }
+    if (i >= n) return;
+    uint32_t n_keep = 0u;
+    if (safety > 0.0f && stats[0] > 0ull) {
+        const float frac = safety * (float)stats[1] * resident_warps / (8.0f * (float)stats[0]);
+        n_keep = frac >= 1.0f ? 0u : n - (uint32_t)ceilf(frac * (float)n);
+    }
+    const uint32_t c = cost[i];
+    cost[i] = 0u;
+    uint32_t key = 0u;
+    if (c > 1u) {
+        const uint32_t e = 31u - (uint32_t)__clz(c);
+        key = 2u * e + ((c >> (e - 1u)) & 1u);   // <= 62
+    }
+    keys[i] = i < n_keep ? 63u : key;
+}
+
+__global__ void iota_kernel(uint32_t* __restrict__ v, uint32_t n) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) v[i] = i;
+}
+
 }  // namespace
+
+void RenderSchedule::release() {
+    if (side) { cudaStreamSynchronize(side); cudaStreamDestroy(side); side = nullptr; }
+    if (ev_rendered) { cudaEventDestroy(ev_rendered); ev_rendered = nullptr; }
+    if (ev_sorted) { cudaEventDestroy(ev_sorted); ev_sorted = nullptr; }
+    void* ps[] = {order, cost, keys, keys_alt, iota, temp, stats};
+    for (void* p : ps) if (p) cudaFree(p);
+    order = cost = keys = keys_alt = iota = nullptr;
+    temp = nullptr; stats = nullptr;
+    cap_blocks = 0; temp_bytes = 0; valid = false; pending = false;
+}
+
+// Make the schedule fit this launch; a launch of another shape (resolution, shard) starts from raster order again.
+static cudaError_t schedule_prepare(RenderSchedule* sch, const DevParams& P, uint32_t n_blocks, cudaStream_t stream) {
+    const bool same = sch->n_blocks == n_blocks && sch->W == P.W && sch->rows == P.n_rows_local && sch->n_shards == P.n_shards &&
+                      sch->shard_index == P.shard_index && sch->tile_rows == P.tile_rows;
+    if (same && sch->order) return cudaSuccess;
+    cudaError_t e;
+    if (n_blocks > sch->cap_blocks || !sch->order) {
+        sch->release();
+        if ((e = cudaStreamCreateWithFlags(&sch->side, cudaStreamNonBlocking)) != cudaSuccess) return e;
+        if ((e = cudaEventCreateWithFlags(&sch->ev_rendered, cudaEventDisableTiming)) != cudaSuccess) return e;
+        if ((e = cudaEventCreateWithFlags(&sch->ev_sorted, cudaEventDisableTiming)) != cudaSuccess) return e;
+        uint32_t** bufs[] = {&sch->order, &sch->cost, &sch->keys, &sch->keys_alt, &sch->iota};
+        for (uint32_t** b : bufs)
+            if ((e = cudaMalloc((void**)b, (size_t)n_blocks * sizeof(uint32_t))) != cudaSuccess) return e;
+        size_t bytes = 0;
+        if ((e = cub::DeviceRadixSort::SortPairsDescending(nullptr, bytes, sch->keys, sch->keys_alt, sch->iota, sch->order,
+                                                           (int)n_blocks, 0, 6, stream)) != cudaSuccess) return e;
+        if ((e = cudaMalloc(&sch->temp, bytes ? bytes : 1)) != cudaSuccess) return e;
+        if ((e = cudaMalloc((void**)&sch->stats, 4 * sizeof(unsigned long long))) != cudaSuccess) return e;
+        sch->temp_bytes = bytes;
+        sch->cap_blocks = n_blocks;
+        iota_kernel<<<(n_blocks + 255u) / 256u, 256, 0, stream>>>(sch->iota, n_blocks);
+    }
+    if ((e = cudaMemsetAsync(sch->cost, 0, (size_t)n_blocks * sizeof(uint32_t), stream)) != cudaSuccess) return e;
+    if ((e = cudaMemsetAsync(sch->stats, 0, 4 * sizeof(unsigned long long), stream)) != cudaSuccess) return e;
+    sch->n_blocks = n_blocks; sch->W = P.W; sch->rows = P.n_rows_local; sch->n_shards = P.n_shards;
+    sch->shard_index = P.shard_index; sch->tile_rows = P.tile_rows;
+    sch->valid = false;
+    return cudaGetLastError();
+}
 
 // scratch = (n_rows_local*W + 2) u32 words: per-pixel accumulators followed by the 64-bit queue head.
 cudaError_t launch_render(const DevScene& sc, const DevParams& P, uint32_t* d_fb, int32_t* d_hit, uint32_t* d_scratch,
-                          DevCounters* d_counters, cudaStream_t stream) {
+                          DevCounters* d_counters, cudaStream_t stream, RenderSchedule* sch) {
     const int tiles_x = (P.W + kTileW - 1) / kTileW, tiles_y = (P.n_rows_local + kTileH - 1) / kTileH;
     const unsigned long long total = (unsigned long long)tiles_x * tiles_y * (kTileW * kTileH * 4);
     if (total == 0) return cudaSuccess;
@@ -202,8 +335,8 @@ cudaError_t launch_render(const DevScene& sc, const DevParams& P, uint32_t* d_fb
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
         int b = 0;
-        e = d_counters ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, render_kernel<true>, kBlock, 0)
-                       : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, render_kernel<false>, kBlock, 0);
+        e = d_counters ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, render_kernel<true, false>, kBlock, 0)
+                       : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, render_kernel<false, true>, kBlock, 0);
         if (e != cudaSuccess) return e;
         blocks_per_sm[which] = b > 0 ? b : 1;
     }
@@ -211,12 +344,53 @@ cudaError_t launch_render(const DevScene& sc, const DevParams& P, uint32_t* d_fb
     const unsigned long long resident = (unsigned long long)n_sm * blocks_per_sm[which];
     const unsigned grid = (unsigned)(want < resident ? want : resident);  // persistent: one wave
     unsigned long long* next = reinterpret_cast<unsigned long long*>(d_scratch + head);
+    const uint32_t n_blocks = (uint32_t)tiles_x * (uint32_t)tiles_y;
+    const bool hint = sch && sch->enabled && !d_counters && RRT_REFILL_MIN == 32 && n_blocks >= sch->min_blocks;
+    if (sch && sch->pending) {   // the previous frame's sort runs on the side stream: this frame starts after it
+        if ((e = cudaStreamWaitEvent(stream, sch->ev_sorted, 0)) != cudaSuccess) return e;
+        sch->pending = false;
+    }
+    if (hint && (e = schedule_prepare(sch, P, n_blocks, stream)) != cudaSuccess) return e;
+    const uint32_t* order = hint && sch->valid ? sch->order : nullptr;
+    uint32_t* cost = hint ? sch->cost : nullptr;
+    unsigned long long* stats = hint ? sch->stats + 2 * (sch->parity & 1) : nullptr;
     if (d_counters)
-        render_kernel<true><<<grid, kBlock, 0, stream>>>(sc, P, d_fb, d_hit, d_scratch, next, d_counters, tiles_x, total);
+        render_kernel<true, false><<<grid, kBlock, 0, stream>>>(sc, P, d_fb, d_hit, d_scratch, next, d_counters, tiles_x, total, nullptr, nullptr);
+    else if (hint)
+        render_kernel<false, true><<<grid, kBlock, 0, stream>>>(sc, P, d_fb, d_hit, d_scratch, next, nullptr, tiles_x, total, order, cost);
     else
-        render_kernel<false><<<grid, kBlock, 0, stream>>>(sc, P, d_fb, d_hit, d_scratch, next, nullptr, tiles_x, total);
+        render_kernel<false, false><<<grid, kBlock, 0, stream>>>(sc, P, d_fb, d_hit, d_scratch, next, nullptr, tiles_x, total, nullptr, nullptr);
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    if (hint) {
+        // next frame's order: stable sort of the blocks by this frame's cost class, on the side stream, so that it
+        // overlaps whatever the caller does with the frame next (copy to the host, gather, L2 flush of a benchmark)
+        cudaStream_t side = sch->side;
+        if ((e = cudaEventRecord(sch->ev_rendered, stream)) != cudaSuccess) return e;
+        if ((e = cudaStreamWaitEvent(side, sch->ev_rendered, 0)) != cudaSuccess) return e;
+        order_stats_kernel<<<(n_blocks + 1023u) / 1024u, 256, 0, side>>>(sch->cost, n_blocks, stats);
+        order_keys_kernel<<<(n_blocks + 255u) / 256u, 256, 0, side>>>(sch->cost, sch->keys, n_blocks, stats,
+                                                                      sch->stats + 2 * (~sch->parity & 1),
+                                                                      (float)grid * (kBlock / 32), sch->tail_safety);
+        sch->parity ^= 1;
+        if ((e = cub::DeviceRadixSort::SortPairsDescending(sch->temp, sch->temp_bytes, sch->keys, sch->keys_alt, sch->iota,
+                                                           sch->order, (int)n_blocks, 0, 6, side)) != cudaSuccess) return e;
+        if ((e = cudaEventRecord(sch->ev_sorted, side)) != cudaSuccess) return e;
+        sch->pending = true;
+        sch->valid = true;
+    }
     return cudaGetLastError();
 }
+
+#if RRT_TIMELINE
+extern "C" int rrt_debug_timeline(unsigned long long* out, int reset) {
+    if (out && cudaMemcpyFromSymbol(out, g_tl, sizeof(g_tl)) != cudaSuccess) return 1;
+    if (reset) {
+        unsigned long long z[4 + 256] = {~0ull, ~0ull, 0ull, 0ull};
+        if (cudaMemcpyToSymbol(g_tl, z, sizeof(z)) != cudaSuccess) return 1;
+    }
+    return 0;
+}
+#endif
 
 size_t render_scratch_words(int n_rows_local, int W) { return (((size_t)n_rows_local * W + 1) & ~(size_t)1) + 2; }
 

@@ -49,6 +49,7 @@ extern "C" {
     pub fn rrt_render_params_default(p: *mut rrt_render_params);
     pub fn rrt_scene_create(desc: *const rrt_scene_desc, device: c_int, out: *mut *mut rrt_scene) -> c_int;
     pub fn rrt_scene_destroy(scene: *mut rrt_scene);
+    pub fn rrt_scene_order_hint(scene: *mut rrt_scene, enable: c_int) -> c_int;
     pub fn rrt_render(scene: *mut rrt_scene, params: *const rrt_render_params, fb_0rgb: *mut u32,
                       hit_ids: *mut i32, device_ms: *mut f32) -> c_int;
     pub fn rrt_render_device(scene: *mut rrt_scene, params: *const rrt_render_params, shard: *const rrt_shard,

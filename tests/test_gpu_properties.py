@@ -200,3 +200,38 @@ def test_peer_frame_two_gpus(rrt):
         pr.join(timeout=120)
         assert pr.exitcode == 0
     assert np.array_equal(out["peer"], out["whole"]) and np.array_equal(out["nccl"], out["whole"])
+
+
+def test_order_hint_changes_nothing(rrt, scenes):
+    # rrt_scene_order_hint: from the second frame of a shape on, the last part of the frame's 16x4-pixel blocks is
+    # handed out heaviest first (cost measured during the previous frame, sorted on a side stream).  Only the ORDER
+    # of the work may change: frames and hit ids must be bit-identical with the hint off, on, after a change of
+    # shape, and when shards of different shapes alternate on one handle.
+    import torch
+    sd = scenes("model2")
+    rt = rrt.RayTracer(sd)
+    L = rrt.abi.lib()
+    rrt.abi.check(L.rrt_scene_order_hint(rt.handle, 0))
+    ref = {}
+    for W, H in ((1920, 1080), (1000, 562)):
+        ref[(W, H)] = render(rrt, rt, W, H, hits=True)
+    rrt.abi.check(L.rrt_scene_order_hint(rt.handle, 1))
+    for W, H in ((1920, 1080), (1920, 1080), (1920, 1080), (1000, 562), (1000, 562), (1920, 1080), (1920, 1080)):
+        fb, hit = render(rrt, rt, W, H, hits=True)
+        assert np.array_equal(fb, ref[(W, H)][0]) and np.array_equal(hit, ref[(W, H)][1])
+    # shards of one frame, alternating on the same handle, each rendered three times into one full frame
+    W, H = 1920, 1080
+    p = rt.params(W, H)
+    fp = C.c_void_p()
+    rrt.abi.check(L.rrt_frame_alloc(0, W, H, C.byref(fp)))
+    for rep in range(3):
+        for r in range(2):
+            sh = rrt.abi.Shard(8, 2, r)
+            for _ in range(3 if rep == 1 else 1):
+                rrt.abi.check(L.rrt_render_device_into_frame(rt.handle, C.byref(p), C.byref(sh), fp, None))
+        out = np.empty((H, W), dtype=np.uint32)
+        rrt.abi.check(L.rrt_copy_frame_to_host(0, fp, W, H, out.ctypes.data, None))
+        torch.cuda.synchronize()
+        assert np.array_equal(out, ref[(W, H)][0])
+    rrt.abi.check(L.rrt_frame_free(0, fp))
+    rt.close()
