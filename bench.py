@@ -244,6 +244,7 @@ def run_gpu(args):
                 host.copy_(sr.frame, non_blocking=True)
             torch.cuda.synchronize(dev)
 
+    step_no[0] = 0 if Wm >= 1 else 1       # c5: walk the same orbit frames as the device-timed leg (warm-up, then K)
     for _ in range(max(1, Wm)):
         e2e_step()
     sync_all()
@@ -285,6 +286,7 @@ def run_gpu(args):
             pass
         a_tf = flops_ray * rays_launch / (kern_ms * 1e-3) / 1e12
         a_gb = bytes_ray * rays_launch / (kern_ms * 1e-3) / 1e9
+        order_hint = os.environ.get("RRT_ORDER_HINT", "1") != "0"
         line = {
             "metric": "Mrays/s (primary rays, 4 per pixel)", "value": value, "unit": "Mrays/s", "n_gpus": world,
             "steps": K, "warmup": Wm, "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "strong",
@@ -295,11 +297,17 @@ def run_gpu(args):
                                         if sr.mode == "peer" else "NCCL all-gather + de-interleave per frame"))
                        if world > 1 else "single GPU",
                        "l2": "flushed (256 MB write) between timed iterations", "octree": stats,
+                       "dispatch_order": ("raster order for the first frame of a shape; afterwards the last part of the frame's "
+                                          "16x4-pixel blocks is handed out heaviest first, by the cost measured while rendering "
+                                          "the previous frame (sorted on a side stream; every sample is traced in full every "
+                                          "frame, results bit-identical with RRT_ORDER_HINT=0)") if order_hint else "raster order",
                        "scene_build_s": round(build_s, 2)},
             "clocks": clocks,
             "e2e": {"value": e2e_val, "unit": "Mrays/s", "h2d_bytes_per_step": C.sizeof(abi.RenderParams),
                     "d2h_bytes_per_step": W * H * 4, "ms_per_step": float(e2e_ms.item()) / K},
-            "gpu_launches": K * (1 + (1 if world > 1 and sr.mode == "nccl" else 0)),
+            # own kernels per step: render_kernel (+ order_stats_kernel, order_keys_kernel of the dispatch-order hint;
+            # the cub radix-sort kernels behind them are library code and not counted) (+ de-interleave after NCCL)
+            "gpu_launches": K * ((3 if order_hint else 1) + (1 if world > 1 and sr.mode == "nccl" else 0)),
             "roofline": {"bound": "fp64", "kernel": "render_kernel", "achieved": a_tf, "peak": fp64.value,
                          "unit": "TFLOP/s", "frac": a_tf / fp64.value, "traffic": traffic,
                          "note": "achieved = REFERENCE-executed flops/ray (SURVEY 8d formula, oracle counters) x rays per launch / "
