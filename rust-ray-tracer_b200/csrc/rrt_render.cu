@@ -345,12 +345,18 @@ cudaError_t launch_render(const DevScene& sc, const DevParams& P, uint32_t* d_fb
     const unsigned grid = (unsigned)(want < resident ? want : resident);  // persistent: one wave
     unsigned long long* next = reinterpret_cast<unsigned long long*>(d_scratch + head);
     const uint32_t n_blocks = (uint32_t)tiles_x * (uint32_t)tiles_y;
-    const bool hint = sch && sch->enabled && !d_counters && RRT_REFILL_MIN == 32 && n_blocks >= sch->min_blocks;
+    bool hint = sch && sch->enabled && !d_counters && RRT_REFILL_MIN == 32 && n_blocks >= sch->min_blocks;
     if (sch && sch->pending) {   // the previous frame's sort runs on the side stream: this frame starts after it
         if ((e = cudaStreamWaitEvent(stream, sch->ev_sorted, 0)) != cudaSuccess) return e;
         sch->pending = false;
     }
-    if (hint && (e = schedule_prepare(sch, P, n_blocks, stream)) != cudaSuccess) return e;
+    if (hint && schedule_prepare(sch, P, n_blocks, stream) != cudaSuccess) {
+        // no memory for the hint's arrays (5 words per block): render in raster order, now and from now on
+        (void)cudaGetLastError();
+        sch->release();
+        sch->enabled = false;
+        hint = false;
+    }
     const uint32_t* order = hint && sch->valid ? sch->order : nullptr;
     uint32_t* cost = hint ? sch->cost : nullptr;
     unsigned long long* stats = hint ? sch->stats + 2 * (sch->parity & 1) : nullptr;
