@@ -80,6 +80,23 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(sm)}
 
 
+def host_threads():
+    """Host threads this process may use (torchrun exports OMP_NUM_THREADS=1 to every rank, which is not the
+    box's core count: the CPU arms and the host-side scene build size their OpenMP teams from this instead)."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
+def set_openmp_threads(n):
+    """omp_set_num_threads for the OpenMP regions of librrt_b200.so (octree build, flatten) called from this thread."""
+    try:
+        C.CDLL("libgomp.so.1").omp_set_num_threads(int(max(1, n)))
+    except OSError:
+        pass
+
+
 def cpu_baseline(sd, params, target_seconds=15.0, threads=0):
     """The oracle (CPU restatement of the reference's rayon path, OpenMP over rows ~ engine.rs:201-203)
     timed on this box's host cores on a BOUNDED sample: a row/column lattice of the same frame sized for
@@ -87,7 +104,7 @@ def cpu_baseline(sd, params, target_seconds=15.0, threads=0):
     from oracle.oracle import OracleScene, lib as olib
     osc = OracleScene(sd)
     W, H = params.width, params.height
-    cores = threads or int(olib().oracle_num_threads())
+    cores = threads or (int(os.environ.get("RRT_CPU_THREADS", "0")) or host_threads())
     # probe on a coarse lattice, then size the real sample
     rs, cs = max(1, H // 64), max(1, W // 128)
     _, _, sec, cnt = osc.render(params, want_hit_ids=False, n_threads=cores, row_step=rs, col_step=cs, counters=True)
@@ -167,6 +184,8 @@ def run_gpu(args):
         dist.init_process_group("nccl", device_id=dev)
 
     desc, W, H = WORKLOADS[args.workload]
+    # host-side scene build (exact octree + culling hierarchies, OpenMP): the ranks of this node share the host cores
+    set_openmp_threads(host_threads() // max(1, int(os.environ.get("LOCAL_WORLD_SIZE", str(world)))))
     sd = load_workload(args.workload)
     t0 = time.time()
     rt = rrt_b200.RayTracer(sd, device=local_rank)
