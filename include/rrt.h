@@ -173,6 +173,15 @@ int rrt_scene_order_hint(rrt_scene* scene, int enable);
 int rrt_render(rrt_scene* scene, const rrt_render_params* params,
                uint32_t* fb_0rgb, int32_t* hit_ids, float* device_ms);
 
+/* A sequence of frames of one scene and one resolution (an orbit, a fly-through; no counterpart in the reference,
+ * whose main.rs draws one frame): frame i is rendered with params[i] and copied to fbs[i] (width*height words each,
+ * layout as rrt_render; pinned host memory makes the copies asynchronous) WHILE frame i+1 renders — two device
+ * frames, a render stream and a copy stream inside the handle.  Synchronous: returns when the last frame is in
+ * host memory.  total_ms (may be NULL) = device time from the first kernel to the last copy.
+ * Each frame is what rrt_render produces for the same params. */
+int rrt_render_frames(rrt_scene* scene, const rrt_render_params* params, int32_t n_frames,
+                      uint32_t* const* fbs, float* total_ms);
+
 /* Device-buffer call: same result written to device memory of the scene's device, enqueued on
  * `cuda_stream` (a cudaStream_t cast to void*, NULL = default stream); does not synchronise.
  * With n_shards > 1 only the owned rows are rendered and written COMPACTLY: owned row k (in

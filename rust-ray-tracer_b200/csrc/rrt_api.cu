@@ -66,6 +66,11 @@ struct rrt_scene {
     size_t fb_cap = 0, hit_cap = 0, scratch_cap = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     RenderSchedule sched;            // dispatch order of the next frame from the measured cost of this one (rrt_render.h)
+    // rrt_render_frames: two device frames, a render and a copy stream, created on first use
+    uint32_t* d_seq_fb[2] = {nullptr, nullptr};
+    size_t seq_cap[2] = {0, 0};
+    cudaStream_t seq_render = nullptr, seq_copy = nullptr;
+    cudaEvent_t seq_rendered[2] = {nullptr, nullptr}, seq_copied[2] = {nullptr, nullptr}, seq_t0 = nullptr, seq_t1 = nullptr;
 
     template <class T>
     int upload(const T* host, size_t n, const T** out) {
@@ -85,6 +90,15 @@ struct rrt_scene {
         if (d_hit) cudaFree(d_hit);
         if (d_scratch) cudaFree(d_scratch);
         sched.release();
+        if (seq_render) { cudaStreamSynchronize(seq_render); cudaStreamDestroy(seq_render); }
+        if (seq_copy) { cudaStreamSynchronize(seq_copy); cudaStreamDestroy(seq_copy); }
+        for (int b = 0; b < 2; ++b) {
+            if (d_seq_fb[b]) cudaFree(d_seq_fb[b]);
+            if (seq_rendered[b]) cudaEventDestroy(seq_rendered[b]);
+            if (seq_copied[b]) cudaEventDestroy(seq_copied[b]);
+        }
+        if (seq_t0) cudaEventDestroy(seq_t0);
+        if (seq_t1) cudaEventDestroy(seq_t1);
         if (ev0) cudaEventDestroy(ev0);
         if (ev1) cudaEventDestroy(ev1);
     }
@@ -409,6 +423,49 @@ int rrt_render(rrt_scene* s, const rrt_render_params* p, uint32_t* fb, int32_t* 
     CU(cudaMemcpy(fb, s->d_fb, n * sizeof(uint32_t), cudaMemcpyDeviceToHost));
     if (hit_ids) CU(cudaMemcpy(hit_ids, s->d_hit, n * 4 * sizeof(int32_t), cudaMemcpyDeviceToHost));
     if (device_ms) CU(cudaEventElapsedTime(device_ms, s->ev0, s->ev1));
+    return RRT_OK;
+}
+
+int rrt_render_frames(rrt_scene* s, const rrt_render_params* params, int32_t n_frames, uint32_t* const* fbs,
+                      float* total_ms) {
+    if (!s || !params || !fbs || n_frames < 0) return fail(RRT_ERR_INVALID, "bad argument");
+    if (n_frames == 0) { if (total_ms) *total_ms = 0.0f; return RRT_OK; }
+    for (int32_t i = 0; i < n_frames; ++i) {
+        if (!fbs[i]) return fail(RRT_ERR_INVALID, "null frame buffer");
+        if (params[i].width != params[0].width || params[i].height != params[0].height)
+            return fail(RRT_ERR_INVALID, "rrt_render_frames: all frames of a sequence have one resolution");
+    }
+    CU(cudaSetDevice(s->device));
+    if (!s->seq_render) {
+        CU(cudaStreamCreateWithFlags(&s->seq_render, cudaStreamNonBlocking));
+        CU(cudaStreamCreateWithFlags(&s->seq_copy, cudaStreamNonBlocking));
+        for (int b = 0; b < 2; ++b) {
+            CU(cudaEventCreateWithFlags(&s->seq_rendered[b], cudaEventDisableTiming));
+            CU(cudaEventCreateWithFlags(&s->seq_copied[b], cudaEventDisableTiming));
+        }
+        CU(cudaEventCreate(&s->seq_t0));
+        CU(cudaEventCreate(&s->seq_t1));
+    }
+    int rc;
+    CU(cudaEventRecord(s->seq_t0, s->seq_render));
+    for (int32_t i = 0; i < n_frames; ++i) {
+        DevParams P;
+        if ((rc = make_params(params + i, nullptr, &P))) return rc;
+        const size_t n = (size_t)P.W * P.H;
+        const int b = i & 1;
+        if ((rc = ensure(&s->d_seq_fb[b], &s->seq_cap[b], n))) return rc;   // no-op after the first two frames
+        if ((rc = ensure(&s->d_scratch, &s->scratch_cap, render_scratch_words(P.n_rows_local, P.W)))) return rc;
+        if (i >= 2) CU(cudaStreamWaitEvent(s->seq_render, s->seq_copied[b], 0));   // frame i-2 has left this buffer
+        CU(launch_render(s->dev, P, s->d_seq_fb[b], nullptr, s->d_scratch, nullptr, s->seq_render, &s->sched));
+        CU(cudaEventRecord(s->seq_rendered[b], s->seq_render));
+        CU(cudaStreamWaitEvent(s->seq_copy, s->seq_rendered[b], 0));
+        CU(cudaMemcpyAsync(fbs[i], s->d_seq_fb[b], n * sizeof(uint32_t), cudaMemcpyDeviceToHost, s->seq_copy));
+        CU(cudaEventRecord(s->seq_copied[b], s->seq_copy));
+    }
+    CU(cudaEventRecord(s->seq_t1, s->seq_copy));
+    CU(cudaStreamSynchronize(s->seq_copy));
+    CU(cudaStreamSynchronize(s->seq_render));
+    if (total_ms) CU(cudaEventElapsedTime(total_ms, s->seq_t0, s->seq_t1));
     return RRT_OK;
 }
 

@@ -243,3 +243,24 @@ class Scene:
                                        None if hit is None else hit.ctypes.data, C.byref(ms)))
         self.hit_ids, self.device_ms = hit, float(ms.value)
         return self.canvas.buffer.reshape(H, W)
+
+    def draw_frames(self, rt: RayTracer, overrides_per_frame, out=None):
+        """A sequence of frames of this resolution (rrt_render_frames): frame i uses rt.params(W, H, **overrides_per_frame[i])
+        and lands in out[i] while frame i+1 renders.  `out`: (n, H, W) u32 array (pinned memory makes the copies
+        asynchronous); allocated if None.  Returns out; self.device_ms = device time of the whole sequence."""
+        W, H = self.canvas.width, self.canvas.height
+        n = len(overrides_per_frame)
+        if out is None:
+            out = np.zeros((n, H, W), dtype=np.uint32)
+        if out.dtype != np.uint32 or out.shape != (n, H, W) or not out.flags["C_CONTIGUOUS"]:
+            raise ValueError("out must be a C-contiguous (n, H, W) uint32 array")
+        params = (abi.RenderParams * max(n, 1))()
+        for i, ov in enumerate(overrides_per_frame):
+            params[i] = rt.params(W, H, **ov)
+        ptrs = (C.c_void_p * max(n, 1))(*[out[i].ctypes.data for i in range(n)])
+        ms = C.c_float(0.0)
+        abi.check(abi.lib().rrt_render_frames(rt.handle, params, n, ptrs, C.byref(ms)))
+        self.device_ms = float(ms.value)
+        if n:
+            self.canvas.buffer = out[n - 1].reshape(-1)
+        return out

@@ -52,6 +52,8 @@ extern "C" {
     pub fn rrt_scene_order_hint(scene: *mut rrt_scene, enable: c_int) -> c_int;
     pub fn rrt_render(scene: *mut rrt_scene, params: *const rrt_render_params, fb_0rgb: *mut u32,
                       hit_ids: *mut i32, device_ms: *mut f32) -> c_int;
+    pub fn rrt_render_frames(scene: *mut rrt_scene, params: *const rrt_render_params, n_frames: i32,
+                             fbs: *const *mut u32, total_ms: *mut f32) -> c_int;
     pub fn rrt_render_device(scene: *mut rrt_scene, params: *const rrt_render_params, shard: *const rrt_shard,
                              d_fb: *mut u32, d_hit_ids: *mut i32, cuda_stream: *mut c_void) -> c_int;
     // multi-GPU: fused render + gather into a (possibly peer-mapped) full frame, include/rrt.h

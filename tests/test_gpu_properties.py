@@ -235,3 +235,27 @@ def test_order_hint_changes_nothing(rrt, scenes):
         assert np.array_equal(out, ref[(W, H)][0])
     rrt.abi.check(L.rrt_frame_free(0, fp))
     rt.close()
+
+
+def test_render_frames_equals_single_frames(rrt, scenes):
+    # rrt_render_frames: frame i is copied to the host while frame i+1 renders (two device frames, render + copy
+    # stream).  Every frame of the sequence must be what rrt_render gives for the same params — with pageable and
+    # with pinned host memory, and with more frames than device buffers.
+    import torch
+    sd = scenes("model2")
+    rt = rrt.RayTracer(sd)
+    W, H = 640, 360
+    cams = []
+    for k in (0, 5, 11, 16, 23):
+        origin, rot = rrt.orbit_camera(k)
+        cams.append(dict(origin=origin, camera_rot=rot))
+    sc = rrt.Scene(W, H)
+    singles = [sc.draw_scene(rt, **c).copy() for c in cams]
+    assert any(not np.array_equal(singles[0], s) for s in singles[1:])
+    seq = rrt.Scene(W, H).draw_frames(rt, cams)
+    pinned = torch.empty((len(cams), H, W), dtype=torch.int32, pin_memory=True)
+    seq_pinned = rrt.Scene(W, H).draw_frames(rt, cams, out=pinned.numpy().view(np.uint32))
+    for i, s in enumerate(singles):
+        assert np.array_equal(seq[i], s) and np.array_equal(seq_pinned[i], s)
+    assert rrt.Scene(W, H).draw_frames(rt, []).shape == (0, H, W)
+    rt.close()
