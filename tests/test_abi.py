@@ -74,6 +74,28 @@ def test_invalid_scene_is_rejected_with_message(rrt):
         rrt.RayTracer(sd)
 
 
+def test_render_frames_argument_checks(rrt):
+    # rrt_render_frames validates the whole sequence before it touches the device or the scene handle, so the
+    # marshalling of the params array / pointer array can be checked without a GPU (a dummy handle is never read).
+    import ctypes as C
+    L = rrt.abi.lib()
+    dummy = (C.c_char * 4096)()
+    h = C.c_void_p(C.addressof(dummy))
+    ms = C.c_float(-1.0)
+    params = (rrt.abi.RenderParams * 3)(*[rrt.make_params(64, 36) for _ in range(3)])
+    bufs = [np.zeros(64 * 36, dtype=np.uint32) for _ in range(3)]
+    ptrs = (C.c_void_p * 3)(*[b.ctypes.data for b in bufs])
+    assert L.rrt_render_frames(h, params, 0, ptrs, C.byref(ms)) == 0 and ms.value == 0.0
+    params[2].height = 40
+    assert L.rrt_render_frames(h, params, 3, ptrs, None) != 0
+    assert b"one resolution" in L.rrt_last_error()
+    params[2].height = 36
+    ptrs[1] = None
+    assert L.rrt_render_frames(h, params, 3, ptrs, None) != 0
+    assert b"null frame buffer" in L.rrt_last_error()
+    assert L.rrt_render_frames(None, params, 3, ptrs, None) != 0
+
+
 def test_no_cpu_fallback_without_device(rrt):
     if has_gpu():
         pytest.skip("a GPU is present")
