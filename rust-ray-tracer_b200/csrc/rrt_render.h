@@ -11,13 +11,14 @@ struct DevParams;
 // Dispatch-order hint carried from one frame of a scene handle to the next.  The persistent kernel ends when its
 // slowest late-fetched warp tile ends (a heavy tile's dependent chain lasts 0.2-0.6 ms where the mean is < 0.1 ms),
 // so every launch records what each 16x4-pixel block cost and the NEXT launch of the same shape hands out the last
-// part of its blocks heaviest first: the tail is then made of the cheapest tiles (order_keys_kernel).  Only the ORDER of the work changes — every
-// sample is traced in full every frame and lands in the same per-pixel accumulator, so frames are bit-identical
-// with and without the hint (tests/test_gpu_properties.py).  The first frame of a shape runs in raster order.
+// part of its blocks heaviest first: the tail is then made of the cheapest tiles (order_keys_kernel).  Only the
+// ORDER of the work changes — every sample is traced in full every frame and lands in the same per-pixel
+// accumulator, so frames are bit-identical with and without the hint (tests/test_gpu_properties.py).  The first
+// frame of a shape runs in raster order.  Measurements: DESIGN.md §6, profiles/r01_v8_c4_drain_timeline.txt.
 struct RenderSchedule {
     uint32_t *order = nullptr, *cost = nullptr, *keys = nullptr, *keys_alt = nullptr, *iota = nullptr;
     void* temp = nullptr;
-    unsigned long long* stats = nullptr;        // 2 x {sum, max} of the tile costs, used alternately
+    unsigned long long* stats = nullptr;        // 2 x {sum, max} of the block costs, used alternately
     int parity = 0;
     cudaStream_t side = nullptr;                // the sort of frame N runs here, behind ev_rendered; frame N+1 waits for ev_sorted
     cudaEvent_t ev_rendered = nullptr, ev_sorted = nullptr;
