@@ -162,12 +162,16 @@ __device__ __forceinline__ bool cull_box(const CullRay& c, float bx0, float by0,
 // compares: left to the compiler the pair is rewritten into an IEEE fmax(tmin, 0) (NaN quieting and all,
 // 8 instructions per child box) followed by a compare.
 __device__ __forceinline__ uint32_t slab_hit_bit(double tmin, double tmax, uint32_t bit) {
+#if defined(__CUDA_ARCH__)
     uint32_t r;
     asm("{\n\t.reg .pred p;\n\tsetp.geu.f64 p, %1, 0d0000000000000000;\n\tsetp.leu.and.f64 p, %2, %1, p;\n\t"
         "selp.u32 %0, %3, 0, p;\n\t}"
         : "=r"(r)
         : "d"(tmax), "d"(tmin), "r"(bit));
     return r;
+#else   // host build of this header (tests/host_emulation): the same predicate in C
+    return (!(tmax < 0.0) && !(tmin > tmax)) ? bit : 0u;
+#endif
 }
 
 // One exact triangle test against the node-local best: strict '<', and on an exact t tie the earlier

@@ -1,0 +1,181 @@
+"""The product's traversal headers compiled for the HOST (tests/host_emulation/emu_trace.cpp) fuzzed against the
+oracle — no GPU needed.  What runs here is the same source the CUDA kernels inline (csrc/rrt_trace.cuh,
+csrc/rrt_device.cuh) over the product's own host octree + flattener (csrc/rrt_octree.cpp): the short-stack walk,
+the FMA quotients, the conservative f32 culling hierarchies / list boxes / subtree boxes and the division-free
+Moller-Trumbore reject must return, bit for bit, what the reference recursion (the oracle) returns
+(DESIGN.md §5).  It is test infrastructure: librrt_b200.so does not contain it and has no CPU fallback
+(tests/test_abi.py::test_no_cpu_fallback_without_device)."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from conftest import random_scene, tiny_scene
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+EMU_DIR = os.path.join(HERE, "host_emulation")
+EMU_SRC = os.path.join(EMU_DIR, "emu_trace.cpp")
+EMU_LIB = os.path.join(EMU_DIR, "libemu_trace.so")
+CSRC = os.path.join(ROOT, "rust-ray-tracer_b200", "csrc")
+
+
+def _build_emu():
+    deps = [EMU_SRC] + [os.path.join(CSRC, f) for f in ("rrt_trace.cuh", "rrt_device.cuh", "rrt_octree.cpp", "rrt_octree.h")]
+    if os.path.exists(EMU_LIB) and all(os.path.getmtime(EMU_LIB) >= os.path.getmtime(d) for d in deps):
+        return
+    flags = ["-O2", "-std=c++17", "-ffp-contract=off", "-fno-fast-math", "-fopenmp", "-fPIC", "-shared", "-w"]
+    try:
+        if " fma " in open("/proc/cpuinfo").read():
+            flags.append("-mfma")          # hardware single-rounding fma(); without it glibc's exact software fma is used
+    except OSError:
+        pass
+    cuda_inc = os.path.join(os.environ.get("CUDA_HOME", "/usr/local/cuda"), "include")
+    subprocess.run(["g++", *flags, "-I" + cuda_inc, "-o", EMU_LIB, EMU_SRC, os.path.join(CSRC, "rrt_octree.cpp")], check=True)
+
+
+@pytest.fixture(scope="module")
+def emu():
+    _build_emu()
+    L = C.CDLL(EMU_LIB)
+    vp, dp = C.c_void_p, C.POINTER(C.c_double)
+    L.emu_scene_create.argtypes = [vp, C.c_uint64, vp, vp, C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.POINTER(vp)]
+    L.emu_scene_destroy.argtypes = [vp]
+    L.emu_scene_destroy.restype = None
+    L.emu_scene_stored.argtypes = [vp]
+    L.emu_scene_stored.restype = C.c_uint64
+    L.emu_scene_planes_safe.argtypes = [vp]
+    L.emu_trace_rays.argtypes = [vp, C.c_uint64, vp, vp, vp, C.c_int, vp, vp]
+    return L
+
+
+class EmuScene:
+    def __init__(self, L, sd, cull_threshold=1, cull_leaf=1, parallel=False, slow_div=False):
+        self.L = L
+        v = np.ascontiguousarray(sd.v, dtype=np.float64)
+        lo, hi = np.asarray(sd.root_min, dtype=np.float64), np.asarray(sd.root_max, dtype=np.float64)
+        h = C.c_void_p()
+        rc = L.emu_scene_create(v.ctypes.data, v.shape[0], lo.ctypes.data, hi.ctypes.data, cull_threshold, cull_leaf,
+                                int(parallel), int(slow_div), C.byref(h))
+        assert rc == 0
+        self.h = h
+
+    def trace(self, o, d, max_t=None, any_hit=False):
+        o = np.ascontiguousarray(o, dtype=np.float64).reshape(-1, 3)
+        d = np.ascontiguousarray(d, dtype=np.float64).reshape(-1, 3)
+        n = o.shape[0]
+        mt = None if max_t is None else np.ascontiguousarray(max_t, dtype=np.float64).reshape(n)
+        tri = np.full(n, -1, dtype=np.int32)
+        tuv = np.zeros((n, 3), dtype=np.float64)
+        assert self.L.emu_trace_rays(self.h, n, o.ctypes.data, d.ctypes.data, None if mt is None else mt.ctypes.data,
+                                     int(any_hit), tri.ctypes.data, tuv.ctypes.data) == 0
+        return tri, tuv
+
+    def close(self):
+        self.L.emu_scene_destroy(self.h)
+
+
+def fuzz_rays(rng, n, centre, extent):
+    """Random rays plus the awkward ones: zero / tiny / huge / non-finite direction components, origins exactly on
+    octree planes and far outside the f32-culling eligibility range, finite and negative max_t."""
+    o = rng.uniform(-extent, extent, (n, 3)) + centre
+    d = rng.normal(size=(n, 3))
+    for k in range(3):
+        d[k::17, k] = 0.0                                   # one zero component
+    d[5::41] = np.eye(3)[rng.integers(0, 3, len(d[5::41]))] * rng.choice([-1.0, 1.0], (len(d[5::41]), 1))  # axis-parallel
+    d[7::53] *= 1e-12                                       # below the culling eligibility range
+    d[11::59] *= 1e12                                       # above it
+    d[13::61, 0] = 1e-300                                   # component whose reciprocal overflows the FMA-quotient range
+    o[3::23] = np.round(o[3::23] / 2.5) * 2.5               # origins ON octree planes of the +-20 root box (k * 2.5)
+    o[9::67] *= 1e4                                         # |origin| far above 16 x scene scale
+    d[19::301, 1] = np.nan
+    d[23::307, 2] = np.inf
+    o[29::311, 0] = -np.inf
+    mt = np.where(rng.random(n) < 0.5, np.inf, rng.uniform(0.05, 3.0 * extent, n))
+    mt[31::97] = -1.0
+    mt[37::101] = np.nan
+    return o, d, mt
+
+
+def check(emu_scene, oracle_scene, o, d, mt, min_hits):
+    tri, tuv = emu_scene.trace(o, d, mt)
+    otri, otuv = oracle_scene.trace(o, d, mt)
+    bad = np.nonzero(tri != otri)[0]
+    assert bad.size == 0, f"{bad.size} hit ids differ, first ray {bad[0]}: {tri[bad[0]]} vs oracle {otri[bad[0]]}"
+    hit = tri >= 0
+    assert np.array_equal(tuv[hit].view(np.uint64), otuv[hit].view(np.uint64))        # t, u, v bit for bit
+    assert hit.sum() >= min_hits
+    # shadow-ray mode: Some / None must agree (which triangle is reported is irrelevant to the caller)
+    atri, _ = emu_scene.trace(o, d, mt, any_hit=True)
+    assert np.array_equal(atri >= 0, otri >= 0)
+
+
+def test_model2_fuzz(emu, scenes):
+    from oracle.oracle import OracleScene
+    sd = scenes("model2")
+    rng = np.random.default_rng(2024)
+    o, d, mt = fuzz_rays(rng, 400_000, np.array([0.0, 3.0, 0.0]), 9.0)
+    o[1::29] = np.array([0.0, 2.0, -10.0])                  # the reference camera
+    osc = OracleScene(sd)
+    for kw in (dict(), dict(slow_div=True), dict(cull_threshold=0), dict(cull_threshold=4, cull_leaf=4), dict(parallel=True)):
+        es = EmuScene(emu, sd, **kw)
+        check(es, osc, o, d, mt, min_hits=30_000)
+        es.close()
+    osc.close()
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_random_soups_fuzz(emu, seed):
+    # many small random scenes: different list lengths, depths, degenerate and duplicate triangles, different scales
+    from oracle.oracle import OracleScene
+    rng = np.random.default_rng(1000 + seed)
+    n = int(rng.choice([1, 2, 9, 60, 400, 3000]))
+    size = float(rng.choice([0.02, 0.3, 1.5, 6.0]))
+    sd = random_scene(n, seed=seed, extent=float(rng.choice([0.5, 6.0, 15.0])), size=size, kr=0.0)
+    if n >= 9:
+        sd.v[3] = sd.v[2]                                   # duplicate triangle: exact t tie, lower id wins
+        sd.v[5, 3:6] = sd.v[5, 0:3]                         # degenerate (zero-length edge)
+        sd.v[7] = np.round(sd.v[7])                         # vertices on integer coordinates (on octree planes)
+    osc = OracleScene(sd)
+    o, d, mt = fuzz_rays(rng, 60_000, np.array([0.0, 2.0, 4.0]), 12.0)
+    # half of the rays aimed at triangle interiors so that small scenes are actually hit
+    k = rng.integers(0, n, len(o) // 2)
+    w = rng.dirichlet([1.0, 1.0, 1.0], len(k))
+    target = (sd.v[k].reshape(-1, 3, 3) * w[:, :, None]).sum(1)
+    sel = np.arange(0, len(o) - 1, 2)[:len(k)]
+    ok = np.isfinite(o[sel]).all(1)
+    d[sel[ok]] = (target[ok] - o[sel[ok]]) * rng.uniform(0.2, 3.0, (ok.sum(), 1))
+    for kw in (dict(), dict(cull_threshold=0), dict(slow_div=True, cull_threshold=2, cull_leaf=2)):
+        es = EmuScene(emu, sd, **kw)
+        check(es, osc, o, d, mt, min_hits=1)
+        es.close()
+    osc.close()
+
+
+def test_planar_grid_ties_and_axis_rays(emu):
+    # a regular grid of coplanar triangles sharing edges and vertices, hit along edges and at vertices by axis-parallel
+    # rays: exact t ties between neighbours (the lower id must win) and slab arithmetic full of 0 * inf
+    from oracle.oracle import OracleScene
+    g = 24
+    xs = np.linspace(-6.0, 6.0, g + 1)
+    tris = []
+    for i in range(g):
+        for j in range(g):
+            a, b, c, e = (xs[i], xs[j], 5.0), (xs[i + 1], xs[j], 5.0), (xs[i], xs[j + 1], 5.0), (xs[i + 1], xs[j + 1], 5.0)
+            tris += [[*a, *b, *c], [*b, *e, *c]]
+    sd = tiny_scene(tris)
+    osc = OracleScene(sd)
+    es = EmuScene(emu, sd)
+    rng = np.random.default_rng(5)
+    n = 40_000
+    gx, gy = rng.integers(0, g + 1, n), rng.integers(0, g + 1, n)
+    o = np.stack([xs[gx], xs[gy], np.full(n, -3.0)], 1)
+    o[::3, 0] += rng.uniform(0, 0.5, len(o[::3]))           # on an edge line, not at a vertex
+    o[1::5] += rng.normal(scale=1e-9, size=(len(o[1::5]), 3))
+    d = np.tile(np.array([0.0, 0.0, 1.0]), (n, 1))
+    d[2::7] = np.array([0.0, 0.0, 2.5])
+    check(es, osc, o, d, np.full(n, np.inf), min_hits=n // 2)
+    es.close()
+    osc.close()
