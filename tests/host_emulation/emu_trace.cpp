@@ -39,13 +39,18 @@ static inline int __double2loint(double d) { return (int)(__double_as_longlong(d
 #endif
 using std::fabs; using std::fma; using std::fmax; using std::fmin; using std::sqrt; using std::pow;
 
-#include "../../rust-ray-tracer_b200/csrc/rrt_trace.cuh"
+#include "../../rust-ray-tracer_b200/csrc/rrt_shade.cuh"   // pulls in rrt_trace.cuh and rrt_device.cuh
 
 namespace {
 struct EmuScene {
     rrt::FlatScene flat;
     rrt::DevScene dev{};
     uint64_t n_nodes_host = 0;
+    // shading side (emu_scene_set_shading): packed exactly as rrt_scene_create packs it (csrc/rrt_api.cu)
+    std::vector<rrt::DevShade> shade;
+    std::vector<rrt::DevMaterial> materials;
+    std::vector<rrt::DevTexture> tex;
+    std::vector<std::vector<uchar4>> texels;
 };
 }  // namespace
 
@@ -82,6 +87,78 @@ void emu_scene_destroy(void* p) { delete static_cast<EmuScene*>(p); }
 
 uint64_t emu_scene_stored(void* p) { return static_cast<EmuScene*>(p)->flat.n_stored; }
 int emu_scene_planes_safe(void* p) { return (int)static_cast<EmuScene*>(p)->dev.planes_safe; }
+
+// shading records, materials and RGB8 textures, packed as rrt_scene_create does (csrc/rrt_api.cu: shading records by
+// original triangle id, DevMaterial field by field, texels widened to RGBX)
+int emu_scene_set_shading(void* p, uint64_t n_tris, const double* vt, const double* vn, const int32_t* material_id,
+                          uint32_t n_materials, const rrt_material* materials, uint32_t n_textures,
+                          const rrt_texture* textures) {
+    EmuScene* s = static_cast<EmuScene*>(p);
+    s->shade.resize(n_tris);
+    for (uint64_t i = 0; i < n_tris; ++i) {
+        const double *n = vn + 9 * i, *t = vt + 6 * i;
+        rrt::DevShade& sh = s->shade[i];
+        std::memcpy(sh.n1, n, 24); std::memcpy(sh.n2, n + 3, 24); std::memcpy(sh.n3, n + 6, 24);
+        std::memcpy(sh.t1, t, 16); std::memcpy(sh.t2, t + 2, 16); std::memcpy(sh.t3, t + 4, 16);
+        sh.material = material_id[i];
+        sh._pad = 0;
+    }
+    s->materials.resize(n_materials);
+    for (uint32_t i = 0; i < n_materials; ++i) {
+        const rrt_material& m = materials[i];
+        rrt::DevMaterial& o = s->materials[i];
+        std::memcpy(o.ka, m.ka, 24); std::memcpy(o.kd, m.kd, 24); std::memcpy(o.ks, m.ks, 24);
+        o.ns = m.ns; o.kr = m.kr; o.tex = m.tex_id; o.bump = m.bump_id;
+    }
+    s->tex.resize(n_textures);
+    s->texels.resize(n_textures);
+    for (uint32_t i = 0; i < n_textures; ++i) {
+        const rrt_texture& t = textures[i];
+        const size_t n = (size_t)t.width * t.height;
+        s->texels[i].resize(n);
+        for (size_t k = 0; k < n; ++k) s->texels[i][k] = make_uchar4(t.rgb[3 * k], t.rgb[3 * k + 1], t.rgb[3 * k + 2], 0);
+        s->tex[i] = rrt::DevTexture{s->texels[i].data(), (uint32_t)t.width, (uint32_t)t.height};
+    }
+    s->dev.shade = s->shade.data();
+    s->dev.materials = s->materials.data();
+    s->dev.tex = s->tex.data();
+    return 0;
+}
+
+// RayTracer::get_ray_colour for n rays through the product's RayStateT state machine (what colour_kernel and
+// render_kernel run per lane).  The fields of DevParams a single ray reads are derived as make_params derives them
+// (csrc/rrt_api.cu: origin, viewport / size, lights, max_depth clamp, surface offset).
+int emu_ray_colours(void* p, const rrt_render_params* rp, uint64_t n, const double* o, const double* d, uint8_t* out_rgb) {
+    const EmuScene* s = static_cast<EmuScene*>(p);
+    if (!s->dev.shade) return 1;
+    rrt::DevParams P{};
+    P.W = rp->width; P.H = rp->height;
+    P.ox = rp->origin[0]; P.oy = rp->origin[1]; P.oz = rp->origin[2];
+    P.xs = rp->viewport[0] / (double)rp->width;
+    P.ys = rp->viewport[1] / (double)rp->height;
+    P.zv = rp->viewport[2];
+    P.n_lights = rp->n_lights;
+    P.max_depth = rp->max_depth > rrt::kMaxReflectDepth ? rrt::kMaxReflectDepth : rp->max_depth;
+    for (int i = 0; i < rp->n_lights; ++i) P.lights[i] = rp->lights[i];
+    P.offset = rp->surface_offset;
+    P.use_rot = rp->use_camera_rot;
+    for (int i = 0; i < 9; ++i) P.rot[i] = rp->camera_rot[i];
+    P.tile_rows = 1; P.n_shards = 1; P.shard_index = 0; P.n_rows_local = rp->height;
+#pragma omp parallel for schedule(dynamic, 256)
+    for (long long i = 0; i < (long long)n; ++i) {
+        rrt::RayStateT<1> st;
+        rrt::TraceCount tc;
+        rrt::Hit h;
+        double park[rrt::kParkWords + 1];
+        st.begin(rrt::V3{o[3 * i], o[3 * i + 1], o[3 * i + 2]}, rrt::V3{d[3 * i], d[3 * i + 1], d[3 * i + 2]});
+        do {
+            rrt::traverse<false>(s->dev, st.so, st.sd, st.smax, st.shadow, h, tc);
+        } while (!st.advance<false>(s->dev, P, h, park));
+        const uint32_t c = st.res;
+        out_rgb[3 * i] = (uint8_t)(c & 255u); out_rgb[3 * i + 1] = (uint8_t)((c >> 8) & 255u); out_rgb[3 * i + 2] = (uint8_t)((c >> 16) & 255u);
+    }
+    return 0;
+}
 
 // Ray::intersect_with_octant_with_max_t for n rays through the product's traverse(); out_tuv as rrt_trace_rays
 int emu_trace_rays(void* p, uint64_t n, const double* o, const double* d, const double* max_t, int any_hit,

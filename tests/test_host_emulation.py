@@ -23,7 +23,8 @@ CSRC = os.path.join(ROOT, "rust-ray-tracer_b200", "csrc")
 
 
 def _build_emu():
-    deps = [EMU_SRC] + [os.path.join(CSRC, f) for f in ("rrt_trace.cuh", "rrt_device.cuh", "rrt_octree.cpp", "rrt_octree.h")]
+    deps = [EMU_SRC, os.path.join(ROOT, "include", "rrt.h")] + [os.path.join(CSRC, f) for f in (
+        "rrt_shade.cuh", "rrt_trace.cuh", "rrt_device.cuh", "rrt_octree.cpp", "rrt_octree.h")]
     if os.path.exists(EMU_LIB) and all(os.path.getmtime(EMU_LIB) >= os.path.getmtime(d) for d in deps):
         return
     flags = ["-O2", "-std=c++17", "-ffp-contract=off", "-fno-fast-math", "-fopenmp", "-fPIC", "-shared", "-w"]
@@ -48,6 +49,8 @@ def emu():
     L.emu_scene_stored.restype = C.c_uint64
     L.emu_scene_planes_safe.argtypes = [vp]
     L.emu_trace_rays.argtypes = [vp, C.c_uint64, vp, vp, vp, C.c_int, vp, vp]
+    L.emu_scene_set_shading.argtypes = [vp, C.c_uint64, vp, vp, vp, C.c_uint32, vp, C.c_uint32, vp]
+    L.emu_ray_colours.argtypes = [vp, vp, C.c_uint64, vp, vp, vp]
     return L
 
 
@@ -61,6 +64,20 @@ class EmuScene:
                                 int(parallel), int(slow_div), C.byref(h))
         assert rc == 0
         self.h = h
+        # shading side: the arrays of the same rrt_scene_desc the library would be given
+        desc, keep = sd.desc()
+        assert L.emu_scene_set_shading(h, sd.n_tris, C.cast(desc.vt, C.c_void_p), C.cast(desc.vn, C.c_void_p),
+                                       C.cast(desc.material_id, C.c_void_p), desc.n_materials,
+                                       C.cast(desc.materials, C.c_void_p), desc.n_textures,
+                                       C.cast(desc.textures, C.c_void_p)) == 0
+        del keep
+
+    def ray_colours(self, params, o, d):
+        o = np.ascontiguousarray(o, dtype=np.float64).reshape(-1, 3)
+        d = np.ascontiguousarray(d, dtype=np.float64).reshape(-1, 3)
+        out = np.zeros((o.shape[0], 3), dtype=np.uint8)
+        assert self.L.emu_ray_colours(self.h, C.byref(params), o.shape[0], o.ctypes.data, d.ctypes.data, out.ctypes.data) == 0
+        return out
 
     def trace(self, o, d, max_t=None, any_hit=False):
         o = np.ascontiguousarray(o, dtype=np.float64).reshape(-1, 3)
@@ -179,3 +196,55 @@ def test_planar_grid_ties_and_axis_rays(emu):
     check(es, osc, o, d, np.full(n, np.inf), min_hits=n // 2)
     es.close()
     osc.close()
+
+
+def camera_rays(rng, n, origin, spread=0.6):
+    o = np.tile(np.asarray(origin, dtype=np.float64), (n, 1))
+    d = np.stack([rng.uniform(-spread, spread, n), rng.uniform(-spread, spread, n), np.ones(n)], 1)
+    return o, d
+
+
+@pytest.mark.parametrize("name", ["model2", "model", "model3"])
+def test_ray_colours_shipped_scenes(emu, rrt, scenes, name):
+    # the whole per-ray path of get_ray_colour (textures, bump maps, ambient / point / directional lights with their
+    # shadow queries, the point-light `break`, mirror bounces with u8 re-quantisation per level) through the product's
+    # RayStateT state machine vs the oracle's recursion: colours must be IDENTICAL
+    from oracle.oracle import OracleScene
+    sd = scenes(name)
+    osc, es = OracleScene(sd), EmuScene(emu, sd)
+    rng = np.random.default_rng(77)
+    L = rrt.Light
+    light_sets = [None, [], [L.Ambient(0.7)], [L.Point(0.9, (0.0, 9.0, -3.0)), L.Ambient(0.3)],
+                  [L.Directional(0.8, (1.0, 2.0, -1.0)), L.Point(0.5, (3.0, 4.0, -8.0)), L.Point(0.5, (-3.0, 1.0, 20.0))]]
+    total_lit = 0
+    for i, lights in enumerate(light_sets):
+        kw = {} if lights is None else dict(lights=lights)
+        for max_depth in ((5, 0, 1) if name == "model2" and i in (0, 3) else (5,)):
+            p = rrt.make_params(320, 180, max_depth=max_depth, **kw)
+            o, d = camera_rays(rng, 40_000, (0.0, 2.0, -10.0))
+            o2, d2, _ = fuzz_rays(rng, 20_000, np.array([0.0, 3.0, 0.0]), 9.0)
+            o, d = np.concatenate([o, o2]), np.concatenate([d, d2])
+            got, want = es.ray_colours(p, o, d), osc.ray_colours(p, o, d)
+            bad = np.nonzero((got != want).any(1))[0]
+            assert bad.size == 0, f"{name} lights#{i} depth {max_depth}: {bad.size} colours differ, first {got[bad[0]]} vs {want[bad[0]]}"
+            total_lit += int((want != 255).any(1).sum())
+    assert total_lit > 50_000
+    es.close()
+    osc.close()
+
+
+def test_ray_colours_random_mirror_scene(emu, rrt):
+    from oracle.oracle import OracleScene
+    for seed, kr, bump in ((1, 0.3, False), (2, 0.9, True), (3, 0.0, True)):
+        sd = random_scene(300, seed=seed, kr=kr)
+        if bump:
+            sd = tiny_scene(sd.v, kr=kr, bump=True)
+        osc, es = OracleScene(sd), EmuScene(emu, sd)
+        rng = np.random.default_rng(seed)
+        p = rrt.make_params(200, 120, max_depth=5)
+        o, d = camera_rays(rng, 60_000, (0.0, 2.0, -10.0), spread=0.9)
+        got, want = es.ray_colours(p, o, d), osc.ray_colours(p, o, d)
+        assert np.array_equal(got, want)
+        assert (want != 255).any(1).sum() > 10_000
+        es.close()
+        osc.close()
