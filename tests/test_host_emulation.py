@@ -248,3 +248,41 @@ def test_ray_colours_random_mirror_scene(emu, rrt):
         assert (want != 255).any(1).sum() > 10_000
         es.close()
         osc.close()
+
+
+def test_config4_sphere_grid_full_size(emu, rrt):
+    # BASELINE configs[3]: the 999 936-triangle sphere grid at full size (parallel octree builder, deep tree, long
+    # node-local lists behind culling hierarchies): traversal bits and colours of camera rays and awkward rays
+    from oracle.oracle import OracleScene
+    from rrt_b200.synthetic import sphere_grid
+    sd = sphere_grid()
+    osc, es = OracleScene(sd), EmuScene(emu, sd, parallel=True)
+    rng = np.random.default_rng(4)
+    o, d = camera_rays(rng, 150_000, (0.0, 2.0, -10.0), spread=0.55)
+    o2, d2, mt2 = fuzz_rays(rng, 50_000, np.array([0.0, 2.0, 8.0]), 10.0)
+    o, d = np.concatenate([o, o2]), np.concatenate([d, d2])
+    mt = np.concatenate([np.full(150_000, np.inf), mt2])
+    check(es, osc, o, d, mt, min_hits=60_000)
+    p = rrt.make_params(3840, 2160)
+    assert np.array_equal(es.ray_colours(p, o[:60_000], d[:60_000]), osc.ray_colours(p, o[:60_000], d[:60_000]))
+    es.close()
+    osc.close()
+
+
+def test_config5_soup_reduced(emu, rrt):
+    # BASELINE configs[4] generator (triangle soup, seed 12345) at 300 000 triangles — the full 10 M scene costs the
+    # oracle ~0.1 s per ray; the 10 M case itself is checked on the GPU against an oracle lattice
+    from oracle.oracle import OracleScene
+    from rrt_b200.synthetic import triangle_soup
+    sd = triangle_soup(n=300_000)
+    osc, es = OracleScene(sd), EmuScene(emu, sd, parallel=True)
+    rng = np.random.default_rng(5)
+    o, d = camera_rays(rng, 20_000, (0.0, 2.0, -10.0), spread=0.8)
+    o2, d2, mt2 = fuzz_rays(rng, 10_000, np.array([0.0, 0.0, 0.0]), 17.0)
+    o, d = np.concatenate([o, o2]), np.concatenate([d, d2])
+    mt = np.concatenate([np.full(20_000, np.inf), mt2])
+    check(es, osc, o, d, mt, min_hits=10_000)
+    p = rrt.make_params(7680, 4320)
+    assert np.array_equal(es.ray_colours(p, o[:8_000], d[:8_000]), osc.ray_colours(p, o[:8_000], d[:8_000]))
+    es.close()
+    osc.close()
