@@ -286,3 +286,30 @@ def test_config5_soup_reduced(emu, rrt):
     assert np.array_equal(es.ray_colours(p, o[:8_000], d[:8_000]), osc.ray_colours(p, o[:8_000], d[:8_000]))
     es.close()
     osc.close()
+
+
+@pytest.mark.parametrize("scale", [1e-6, 1e-3, 1e3, 1e7])
+def test_scene_scale_invariance_of_the_culling_budget(emu, scale):
+    # the f32 culling boxes are padded and the ray eligibility is decided RELATIVE to the scene's coordinate scale
+    # (rrt_octree.h kCullPadRel / kCullOriginRel): the same scene and rays scaled by 1e-6 .. 1e7 (root box included)
+    # must still match the oracle bit for bit, with and without off-centre placement
+    from oracle.oracle import OracleScene
+    for shift in (0.0, 0.37):
+        sd = random_scene(800, seed=11, extent=6.0, size=1.2, kr=0.0)
+        sd.v = np.ascontiguousarray((sd.v + shift) * scale)
+        sd.root_min = tuple((-20.0 + shift) * scale for _ in range(3))
+        sd.root_max = tuple((20.0 + shift) * scale for _ in range(3))
+        osc, es = OracleScene(sd), EmuScene(emu, sd)
+        rng = np.random.default_rng(3)
+        o, d, mt = fuzz_rays(rng, 80_000, np.array([0.0, 2.0, 4.0]), 12.0)
+        k = rng.integers(0, sd.n_tris, len(o) // 2)
+        w = rng.dirichlet([1.0, 1.0, 1.0], len(k))
+        target = (sd.v[k].reshape(-1, 3, 3) * w[:, :, None]).sum(1) / scale
+        sel = np.arange(0, len(o) - 1, 2)[:len(k)]
+        ok = np.isfinite(o[sel]).all(1)
+        d[sel[ok]] = target[ok] - o[sel[ok]]
+        o = (o + shift) * scale
+        d = d * rng.choice([1.0, scale, 1.0 / scale], (len(d), 1))
+        check(es, osc, o, d, mt * scale, min_hits=5_000)
+        es.close()
+        osc.close()
