@@ -446,25 +446,32 @@ int rrt_render_frames(rrt_scene* s, const rrt_render_params* params, int32_t n_f
         CU(cudaEventCreate(&s->seq_t0));
         CU(cudaEventCreate(&s->seq_t1));
     }
-    int rc;
-    CU(cudaEventRecord(s->seq_t0, s->seq_render));
-    for (int32_t i = 0; i < n_frames; ++i) {
-        DevParams P;
-        if ((rc = make_params(params + i, nullptr, &P))) return rc;
-        const size_t n = (size_t)P.W * P.H;
-        const int b = i & 1;
-        if ((rc = ensure(&s->d_seq_fb[b], &s->seq_cap[b], n))) return rc;   // no-op after the first two frames
-        if ((rc = ensure(&s->d_scratch, &s->scratch_cap, render_scratch_words(P.n_rows_local, P.W)))) return rc;
-        if (i >= 2) CU(cudaStreamWaitEvent(s->seq_render, s->seq_copied[b], 0));   // frame i-2 has left this buffer
-        CU(launch_render(s->dev, P, s->d_seq_fb[b], nullptr, s->d_scratch, nullptr, s->seq_render, &s->sched));
-        CU(cudaEventRecord(s->seq_rendered[b], s->seq_render));
-        CU(cudaStreamWaitEvent(s->seq_copy, s->seq_rendered[b], 0));
-        CU(cudaMemcpyAsync(fbs[i], s->d_seq_fb[b], n * sizeof(uint32_t), cudaMemcpyDeviceToHost, s->seq_copy));
-        CU(cudaEventRecord(s->seq_copied[b], s->seq_copy));
-    }
-    CU(cudaEventRecord(s->seq_t1, s->seq_copy));
-    CU(cudaStreamSynchronize(s->seq_copy));
-    CU(cudaStreamSynchronize(s->seq_render));
+    // enqueue everything; whatever happens, nothing may still be writing to the caller's buffers on return
+    auto enqueue = [&]() -> int {
+        int rc;
+        CU(cudaEventRecord(s->seq_t0, s->seq_render));
+        for (int32_t i = 0; i < n_frames; ++i) {
+            DevParams P;
+            if ((rc = make_params(params + i, nullptr, &P))) return rc;
+            const size_t n = (size_t)P.W * P.H;
+            const int b = i & 1;
+            if ((rc = ensure(&s->d_seq_fb[b], &s->seq_cap[b], n))) return rc;   // no-op after the first two frames
+            if ((rc = ensure(&s->d_scratch, &s->scratch_cap, render_scratch_words(P.n_rows_local, P.W)))) return rc;
+            if (i >= 2) CU(cudaStreamWaitEvent(s->seq_render, s->seq_copied[b], 0));   // frame i-2 has left this buffer
+            CU(launch_render(s->dev, P, s->d_seq_fb[b], nullptr, s->d_scratch, nullptr, s->seq_render, &s->sched));
+            CU(cudaEventRecord(s->seq_rendered[b], s->seq_render));
+            CU(cudaStreamWaitEvent(s->seq_copy, s->seq_rendered[b], 0));
+            CU(cudaMemcpyAsync(fbs[i], s->d_seq_fb[b], n * sizeof(uint32_t), cudaMemcpyDeviceToHost, s->seq_copy));
+            CU(cudaEventRecord(s->seq_copied[b], s->seq_copy));
+        }
+        CU(cudaEventRecord(s->seq_t1, s->seq_copy));
+        return RRT_OK;
+    };
+    const int rc = enqueue();
+    const cudaError_t e_render = cudaStreamSynchronize(s->seq_render), e_copy = cudaStreamSynchronize(s->seq_copy);
+    if (rc) return rc;
+    CU(e_render);
+    CU(e_copy);
     if (total_ms) CU(cudaEventElapsedTime(total_ms, s->seq_t0, s->seq_t1));
     return RRT_OK;
 }
