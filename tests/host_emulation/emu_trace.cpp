@@ -160,6 +160,22 @@ int emu_ray_colours(void* p, const rrt_render_params* rp, uint64_t n, const doub
     return 0;
 }
 
+// work counters of the walk, summed over n rays: out[4] = exact M-T tests, child-slab tests, culling-box tests, nodes
+int emu_trace_counts(void* p, uint64_t n, const double* o, const double* d, int any_hit, uint64_t* out) {
+    const EmuScene* s = static_cast<EmuScene*>(p);
+    uint64_t mt = 0, box = 0, cull = 0, nodes = 0;
+#pragma omp parallel for schedule(dynamic, 256) reduction(+ : mt, box, cull, nodes)
+    for (long long i = 0; i < (long long)n; ++i) {
+        rrt::Hit h;
+        rrt::TraceCount tc;
+        rrt::traverse<true>(s->dev, rrt::V3{o[3 * i], o[3 * i + 1], o[3 * i + 2]}, rrt::V3{d[3 * i], d[3 * i + 1], d[3 * i + 2]},
+                            __longlong_as_double(0x7FF0000000000000ll), any_hit != 0, h, tc);
+        mt += tc.mt; box += tc.box; cull += tc.cull; nodes += tc.nodes;
+    }
+    out[0] = mt; out[1] = box; out[2] = cull; out[3] = nodes;
+    return 0;
+}
+
 // Ray::intersect_with_octant_with_max_t for n rays through the product's traverse(); out_tuv as rrt_trace_rays
 int emu_trace_rays(void* p, uint64_t n, const double* o, const double* d, const double* max_t, int any_hit,
                    int32_t* out_tri, double* out_tuv) {
