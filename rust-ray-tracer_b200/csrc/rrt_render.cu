@@ -1,7 +1,7 @@
 // rrt_render.cu — kernels for Scene::draw_scene (engine.rs:186-255) on sm_100a and their launchers.
 // Compiled with -fmad=false -prec-div=true -prec-sqrt=true (no fast-math anywhere).
 #include "rrt_render.h"
-#include "rrt_shade.cuh"
+#include "rrt_raygen.cuh"
 
 #include <cub/device/device_radix_sort.cuh>
 
@@ -20,9 +20,6 @@ namespace {
                              // tile (x4 supersamples) together through its shadow / mirror rays (sweep: profiles/r01_experiments.md)
 #endif
 constexpr int kBlock = RRT_BLOCK;
-constexpr int kTileW = 16;       // samples are enumerated in 16x4-pixel blocks of eight 4x2-pixel tiles,
-constexpr int kTileH = 4;        // 4 supersamples per pixel: 32 consecutive indices = one 8x4 half-pixel lattice
-
 #ifndef RRT_TIMELINE
 #define RRT_TIMELINE 0      // development aid (tools/drain_timeline.py): when does the queue run dry, when do warps exit
 #endif
@@ -30,13 +27,6 @@ constexpr int kTileH = 4;        // 4 supersamples per pixel: 32 consecutive ind
 __device__ unsigned long long g_tl[4 + 256];   // [0] min start, [1] min queue-dry, [2] max exit, [3] warps; [4..] exits per 5 us after queue-dry
 __device__ __forceinline__ unsigned long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
 #endif
-
-// compact row k of this shard -> buffer row (rrt_shard in rrt.h)
-__device__ __forceinline__ int buffer_row(const DevParams& P, int k) {
-    if (P.n_shards <= 1) return k;
-    const int jl = k / P.tile_rows, within = k - jl * P.tile_rows;
-    return (P.shard_index + jl * P.n_shards) * P.tile_rows + within;
-}
 
 // Persistent render kernel (Scene::draw_scene, engine.rs:186-255).  One lane = one supersample at a time.
 // Whenever lanes of a warp run dry — their ray missed, or finished its shadow / mirror chain early — they
@@ -93,32 +83,18 @@ render_kernel(const DevScene sc, const __grid_constant__ DevParams P, uint32_t* 
                 const unsigned long long s = base + __popc(idle & lt_mask);
                 if (s < total) {
                     const unsigned long long tile = s >> 5;
-                    const unsigned l = (unsigned)s & 31u, p = l >> 2;
+                    const unsigned l = (unsigned)s & 31u;
                     unsigned long long blk = tile >> 3;
                     if (HINT && order) blk = __ldg(order + blk);   // the last part of the frame: heaviest blocks first
                     if (HINT && lane == 0) tile_info = make_uint2((uint32_t)blk, (uint32_t)clock());   // one tile per fetch
-                    const unsigned w = (unsigned)tile & 7u;
-                    const int by = (int)(blk / (unsigned)tiles_x), bx = (int)(blk - (unsigned long long)by * tiles_x);
-                    const int col = bx * kTileW + (int)(w & 3u) * 4 + (int)(p & 3u);
-                    const int krow = by * kTileH + (int)(w >> 2) * 2 + (int)(p >> 2);
-                    k = l & 3u;
+                    int col, krow;
+                    sample_pixel(blk, (unsigned)tile & 7u, l, tiles_x, col, krow, k);
                     if (col < P.W && krow < P.n_rows_local) {
                         pix = (size_t)krow * P.W + col;
                         const int r = buffer_row(P, krow);
                         out = P.full_frame ? (size_t)r * P.W + col : pix;
-                        // put_pixel: new_x = x + W/2, new_y = H - (y + H/2)  (engine.rs:147-150)
-                        const int x = col - P.W / 2;
-                        const int y = P.H - r - P.H / 2;
-                        const bool traced = r >= 1 && r < P.H && col < 2 * (P.W / 2) && y >= -(P.H / 2) && y < P.H / 2;
-                        if (traced) {
-                            const double fx = (k & 1u) ? ((double)x + 0.5) : (double)x;   // engine.rs:208,218
-                            const double fy = (k & 2u) ? ((double)y + 0.5) : (double)y;   // engine.rs:209,226
-                            V3 d{fx * P.xs, fy * P.ys, P.zv};
-                            if (P.use_rot) {  // extension (rrt.h): d' = R d
-                                d = V3{(P.rot[0] * d.x + P.rot[1] * d.y) + P.rot[2] * d.z,
-                                       (P.rot[3] * d.x + P.rot[4] * d.y) + P.rot[5] * d.z,
-                                       (P.rot[6] * d.x + P.rot[7] * d.y) + P.rot[8] * d.z};
-                            }
+                        V3 d;
+                        if (primary_ray(P, col, r, k, d)) {
                             st.begin(V3{P.ox, P.oy, P.oz}, d);
                             active = true;
                             if (COUNT) n_primary++;
@@ -142,14 +118,9 @@ render_kernel(const DevScene sc, const __grid_constant__ DevParams P, uint32_t* 
             if (st.advance<COUNT>(sc, P, h, park)) {
                 active = false;
                 if (hit_ids) hit_ids[pix * 4 + k] = st.hit0;
-                const uint32_t c = st.res;
-                const uint32_t add = (c & 255u) | (((c >> 8) & 255u) << 10) | (((c >> 16) & 255u) << 20) | (1u << 30);
+                const uint32_t add = sample_add(st.res);
                 const uint32_t old = atomicAdd(acc + pix, add);
-                if ((old >> 30) == 3u) {  // 4th sample of this pixel: Color::mix + pack (entities.rs:32-36,49-69)
-                    const uint32_t sum = old + add;
-                    const uint32_t r = (sum & 1023u) >> 2, g = ((sum >> 10) & 1023u) >> 2, b = ((sum >> 20) & 1023u) >> 2;
-                    fb[out] = b + (g << 8) + (r << 16);
-                }
+                if ((old >> 30) == 3u) fb[out] = mix_pack(old + add);  // 4th sample of this pixel: Color::mix + pack
             }
         }
     }

@@ -9,6 +9,7 @@
 // Arithmetic: the same IEEE double / float operations — g++ -O2 -ffp-contract=off -mfma, fma()/fmaf() are the
 // hardware's single-rounding instructions exactly like DFMA / FFMA, fmin/fmax/fminf/fmaxf follow the same
 // "NaN loses" rule as CUDA's.
+#include <algorithm>
 #include <cmath>
 #include <cstdint>
 #include <cstring>
@@ -39,7 +40,7 @@ static inline int __double2loint(double d) { return (int)(__double_as_longlong(d
 #endif
 using std::fabs; using std::fma; using std::fmax; using std::fmin; using std::sqrt; using std::pow;
 
-#include "../../rust-ray-tracer_b200/csrc/rrt_shade.cuh"   // pulls in rrt_trace.cuh and rrt_device.cuh
+#include "../../rust-ray-tracer_b200/csrc/rrt_raygen.cuh"   // pulls in rrt_shade.cuh, rrt_trace.cuh and rrt_device.cuh
 
 namespace {
 struct EmuScene {
@@ -53,6 +54,29 @@ struct EmuScene {
     std::vector<std::vector<uchar4>> texels;
 };
 }  // namespace
+
+// The fields of DevParams derived as make_params derives them (csrc/rrt_api.cu: origin, viewport / size, lights,
+// max_depth clamp, surface offset, rotation, shard and its row count as rrt_shard_rows counts them).
+static rrt::DevParams emu_params(const rrt_render_params* rp, int tile_rows, int n_shards, int shard_index) {
+    rrt::DevParams P{};
+    P.W = rp->width; P.H = rp->height;
+    P.ox = rp->origin[0]; P.oy = rp->origin[1]; P.oz = rp->origin[2];
+    P.xs = rp->viewport[0] / (double)rp->width;
+    P.ys = rp->viewport[1] / (double)rp->height;
+    P.zv = rp->viewport[2];
+    P.n_lights = rp->n_lights;
+    P.max_depth = rp->max_depth > rrt::kMaxReflectDepth ? rrt::kMaxReflectDepth : rp->max_depth;
+    for (int i = 0; i < rp->n_lights; ++i) P.lights[i] = rp->lights[i];
+    P.offset = rp->surface_offset;
+    P.use_rot = rp->use_camera_rot;
+    for (int i = 0; i < 9; ++i) P.rot[i] = rp->camera_rot[i];
+    P.tile_rows = tile_rows; P.n_shards = n_shards; P.shard_index = shard_index;
+    int rows = 0;
+    if (n_shards <= 1) rows = rp->height;
+    else for (int j = shard_index; (int64_t)j * tile_rows < rp->height; j += n_shards) rows += std::min(tile_rows, rp->height - j * tile_rows);
+    P.n_rows_local = rows;
+    return P;
+}
 
 extern "C" {
 
@@ -131,19 +155,7 @@ int emu_scene_set_shading(void* p, uint64_t n_tris, const double* vt, const doub
 int emu_ray_colours(void* p, const rrt_render_params* rp, uint64_t n, const double* o, const double* d, uint8_t* out_rgb) {
     const EmuScene* s = static_cast<EmuScene*>(p);
     if (!s->dev.shade) return 1;
-    rrt::DevParams P{};
-    P.W = rp->width; P.H = rp->height;
-    P.ox = rp->origin[0]; P.oy = rp->origin[1]; P.oz = rp->origin[2];
-    P.xs = rp->viewport[0] / (double)rp->width;
-    P.ys = rp->viewport[1] / (double)rp->height;
-    P.zv = rp->viewport[2];
-    P.n_lights = rp->n_lights;
-    P.max_depth = rp->max_depth > rrt::kMaxReflectDepth ? rrt::kMaxReflectDepth : rp->max_depth;
-    for (int i = 0; i < rp->n_lights; ++i) P.lights[i] = rp->lights[i];
-    P.offset = rp->surface_offset;
-    P.use_rot = rp->use_camera_rot;
-    for (int i = 0; i < 9; ++i) P.rot[i] = rp->camera_rot[i];
-    P.tile_rows = 1; P.n_shards = 1; P.shard_index = 0; P.n_rows_local = rp->height;
+    const rrt::DevParams P = emu_params(rp, 1, 1, 0);
 #pragma omp parallel for schedule(dynamic, 256)
     for (long long i = 0; i < (long long)n; ++i) {
         rrt::RayStateT<1> st;
@@ -156,6 +168,56 @@ int emu_ray_colours(void* p, const rrt_render_params* rp, uint64_t n, const doub
         } while (!st.advance<false>(s->dev, P, h, park));
         const uint32_t c = st.res;
         out_rgb[3 * i] = (uint8_t)(c & 255u); out_rgb[3 * i + 1] = (uint8_t)((c >> 8) & 255u); out_rgb[3 * i + 2] = (uint8_t)((c >> 16) & 255u);
+    }
+    return 0;
+}
+
+// One shard of one frame the way render_kernel produces it, minus the warps: every position of the sample queue is
+// decoded with the kernel's own sample_pixel / buffer_row / primary_ray, traced and shaded through RayStateT, and merged
+// through the kernel's packed per-pixel accumulator (sample_add / mix_pack).  full_frame != 0: fb is the whole frame and
+// owned rows go to their buffer rows (rrt_render_device_into_frame); else fb holds the shard's rows compactly.
+// hit_ids (may be NULL): [rows][W][4] in the same row numbering as fb... of the COMPACT rows, as the kernel writes them.
+int emu_render_shard(void* p, const rrt_render_params* rp, int tile_rows, int n_shards, int shard_index, int full_frame,
+                     uint32_t* fb, int32_t* hit_ids) {
+    const EmuScene* s = static_cast<EmuScene*>(p);
+    if (!s->dev.shade) return 1;
+    rrt::DevParams P = emu_params(rp, tile_rows, n_shards, shard_index);
+    P.full_frame = full_frame;
+    const int tiles_x = (P.W + rrt::kTileW - 1) / rrt::kTileW, tiles_y = (P.n_rows_local + rrt::kTileH - 1) / rrt::kTileH;
+    const long long n_tiles = (long long)tiles_x * tiles_y * 8;
+    std::vector<uint32_t> acc((size_t)P.n_rows_local * P.W, 0u);
+#pragma omp parallel for schedule(dynamic, 16)
+    for (long long tile = 0; tile < n_tiles; ++tile) {
+        for (unsigned l = 0; l < 32; ++l) {
+            int col, krow;
+            unsigned k;
+            rrt::sample_pixel((unsigned long long)(tile >> 3), (unsigned)tile & 7u, l, tiles_x, col, krow, k);
+            if (!(col < P.W && krow < P.n_rows_local)) continue;
+            const size_t pix = (size_t)krow * P.W + col;
+            const int r = rrt::buffer_row(P, krow);
+            const size_t out = P.full_frame ? (size_t)r * P.W + col : pix;
+            rrt::V3 d;
+            uint32_t add;
+            if (rrt::primary_ray(P, col, r, k, d)) {
+                rrt::RayStateT<1> st;
+                rrt::TraceCount tc;
+                rrt::Hit h;
+                double park[rrt::kParkWords + 1];
+                st.begin(rrt::V3{P.ox, P.oy, P.oz}, d);
+                do {
+                    rrt::traverse<false>(s->dev, st.so, st.sd, st.smax, st.shadow, h, tc);
+                } while (!st.advance<false>(s->dev, P, h, park));
+                if (hit_ids) hit_ids[pix * 4 + k] = st.hit0;
+                add = rrt::sample_add(st.res);
+            } else {
+                if (hit_ids) hit_ids[pix * 4 + k] = -1;
+                add = 1u << 30;
+            }
+            // the four samples of a pixel sit in one tile, i.e. in this thread: no atomics needed here
+            const uint32_t old = acc[pix];
+            acc[pix] = old + add;
+            if ((old >> 30) == 3u) fb[out] = (add == (1u << 30)) ? 0u : rrt::mix_pack(old + add);
+        }
     }
     return 0;
 }

@@ -23,8 +23,8 @@ CSRC = os.path.join(ROOT, "rust-ray-tracer_b200", "csrc")
 
 
 def _build_emu():
-    deps = [EMU_SRC, os.path.join(ROOT, "include", "rrt.h")] + [os.path.join(CSRC, f) for f in (
-        "rrt_shade.cuh", "rrt_trace.cuh", "rrt_device.cuh", "rrt_octree.cpp", "rrt_octree.h")]
+    deps = [EMU_SRC, os.path.join(ROOT, "include", "rrt.h")] + [
+        os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h", ".cpp"))]
     if os.path.exists(EMU_LIB) and all(os.path.getmtime(EMU_LIB) >= os.path.getmtime(d) for d in deps):
         return
     flags = ["-O2", "-std=c++17", "-ffp-contract=off", "-fno-fast-math", "-fopenmp", "-fPIC", "-shared", "-w"]
@@ -51,6 +51,7 @@ def emu():
     L.emu_trace_rays.argtypes = [vp, C.c_uint64, vp, vp, vp, C.c_int, vp, vp]
     L.emu_scene_set_shading.argtypes = [vp, C.c_uint64, vp, vp, vp, C.c_uint32, vp, C.c_uint32, vp]
     L.emu_ray_colours.argtypes = [vp, vp, C.c_uint64, vp, vp, vp]
+    L.emu_render_shard.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp]
     return L
 
 
@@ -89,6 +90,17 @@ class EmuScene:
         assert self.L.emu_trace_rays(self.h, n, o.ctypes.data, d.ctypes.data, None if mt is None else mt.ctypes.data,
                                      int(any_hit), tri.ctypes.data, tuv.ctypes.data) == 0
         return tri, tuv
+
+    def render_shard(self, params, tile_rows=1, n_shards=1, shard_index=0, full_frame=None, want_hit_ids=True):
+        """-> (fb, hit): the shard's rows compactly (rows, W), or written into `full_frame` (H, W) when given."""
+        from rrt_b200.sharding import owned_rows
+        W, H = params.width, params.height
+        rows = H if n_shards <= 1 else len(owned_rows(H, tile_rows, n_shards, shard_index))
+        fb = np.zeros((rows, W), dtype=np.uint32) if full_frame is None else full_frame
+        hit = np.full((rows, W, 4), -7, dtype=np.int32) if want_hit_ids else None
+        assert self.L.emu_render_shard(self.h, C.byref(params), tile_rows, n_shards, shard_index, int(full_frame is not None),
+                                       fb.ctypes.data, None if hit is None else hit.ctypes.data) == 0
+        return fb, hit
 
     def close(self):
         self.L.emu_scene_destroy(self.h)
@@ -313,3 +325,44 @@ def test_scene_scale_invariance_of_the_culling_budget(emu, scale):
         check(es, osc, o, d, mt * scale, min_hits=5_000)
         es.close()
         osc.close()
+
+
+@pytest.mark.parametrize("W,H", [(160, 90), (161, 91), (97, 64), (16, 4), (5, 3), (33, 2), (1, 1)])
+def test_frames_through_the_kernel_helpers(emu, rrt, scenes, W, H):
+    # whole frames the way render_kernel assembles them — queue position -> pixel / supersample (sample_pixel),
+    # put_pixel mapping and the rows / columns the reference never writes (primary_ray), the packed per-pixel
+    # accumulator and Color::mix (sample_add / mix_pack), all from csrc/rrt_raygen.cuh — against the oracle's
+    # draw_scene: frame words and the depth-0 hit id of every supersample, odd and tiny sizes included
+    from oracle.oracle import OracleScene
+    sd = scenes("model2")
+    osc, es = OracleScene(sd), EmuScene(emu, sd)
+    origin, rot = rrt.orbit_camera(7)
+    for kw in (dict(), dict(origin=origin, camera_rot=rot)):
+        p = rrt.make_params(W, H, **kw)
+        fb, hit = es.render_shard(p)
+        ofb, ohit, _, _ = osc.render(p)
+        assert np.array_equal(fb, ofb)
+        assert np.array_equal(hit, ohit)
+    es.close()
+    osc.close()
+
+
+@pytest.mark.parametrize("W,H,T,G", [(96, 70, 8, 2), (64, 45, 3, 3), (50, 37, 8, 8), (40, 9, 8, 4)])
+def test_shards_through_the_kernel_helpers(emu, rrt, scenes, W, H, T, G):
+    # interleaved tile-row shards (buffer_row): compact shards are the owned rows of the whole frame, and shards stored
+    # straight into one full frame (rrt_render_device_into_frame's mode) reassemble it; ranks without rows included
+    from oracle.oracle import OracleScene
+    from rrt_b200.sharding import owned_rows
+    sd = scenes("model2")
+    osc, es = OracleScene(sd), EmuScene(emu, sd)
+    p = rrt.make_params(W, H)
+    ofb, ohit, _, _ = osc.render(p)
+    frame = np.zeros((H, W), dtype=np.uint32)
+    for r in range(G):
+        rows = owned_rows(H, T, G, r)
+        fb, hit = es.render_shard(p, T, G, r)
+        assert np.array_equal(fb, ofb[rows]) and np.array_equal(hit, ohit[rows])
+        es.render_shard(p, T, G, r, full_frame=frame, want_hit_ids=False)
+    assert np.array_equal(frame, ofb)
+    es.close()
+    osc.close()
