@@ -20,6 +20,16 @@ struct TraceCount {
     uint32_t mt = 0, box = 0, cull = 0, nodes = 0;
 };
 
+// Development aid: tools/walk_stats.py compiles this header for the HOST with -DRRT_WALK_STATS and collects
+// histograms of the walk (how many children a visited node keeps / the exact slabs hit / survive their subtree
+// boxes, how long the culling walks are).  Never defined in a product build: the hooks expand to nothing.
+#ifdef RRT_WALK_STATS
+void rrt_walk_stat(int kind, unsigned value);
+#define RRT_STAT(kind, value) rrt_walk_stat(kind, (unsigned)(value))
+#else
+#define RRT_STAT(kind, value) ((void)0)
+#endif
+
 // min/max for operands known not to be NaN (one compare + selects instead of the IEEE fmin/fmax
 // sequence).  Which of +0/-0 comes back is irrelevant: results only feed comparisons.
 __device__ __forceinline__ double min_nn(double a, double b) { return b < a ? b : a; }
@@ -278,6 +288,9 @@ __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const 
             uint32_t cur = __ldg(&n->cull_root);
             int csp = 0;
             bool live = true;
+#ifdef RRT_WALK_STATS
+            unsigned ws_inner = 0, ws_leaf = 0, ws_first = 0;
+#endif
             while (live) {
 #if RRT_CULL_LOOP == 2
                 while (live && !(cur & kLeafBit)) {
@@ -289,6 +302,9 @@ __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const 
 #endif
                     const DevCull* __restrict__ c = sc.cull + cur;
                     bool go0, go1, swap;
+#ifdef RRT_WALK_STATS
+                    ws_inner++;
+#endif
                     if (COUNT) tc.cull += 2;
 #if RRT_CULL_F32
                     const float4* bp = reinterpret_cast<const float4*>(c);
@@ -346,6 +362,10 @@ __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const 
                         if (COUNT) tc.mt++;
                         upd |= test_record(o, d, sc.tris, first + i, nb);
                     }
+#ifdef RRT_WALK_STATS
+                    ws_leaf++;
+                    if (upd && !ws_first) ws_first = ws_inner + 1;   // inner steps before the first accepted record (+1)
+#endif
                     if (any_hit && nb.id != kNone && nb.t < best.t) break;  // best will improve => Some
 #if RRT_CULL_F32
                     if (upd) limit = __double2float_ru(nb.t);
@@ -354,7 +374,11 @@ __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const 
                     else live = false;
                 }
             }
+            RRT_STAT(3, ws_inner);
+            RRT_STAT(4, ws_leaf);
+            RRT_STAT(5, ws_first);
         }
+        RRT_STAT(6, (m.w != 0u ? 1u : 0u) | (m.y != 0u ? 2u : 0u) | (nb.id != kNone ? 4u : 0u));
         if (nb.id != kNone) {
             sp = 0;  // this node returns Some: every pending sibling, at every level, is dead
             lv_ord = 0;
@@ -398,6 +422,8 @@ __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const 
             }
             hitmask &= m.y;
             if (COUNT) tc.box += __popc(m.y);
+            RRT_STAT(0, __popc(m.y));
+            RRT_STAT(1, __popc(hitmask));
 #if RRT_CULL_F32 && RRT_SUB_BOX == 2
             // A child whose SUBTREE box (own list + all descendants, padded f32, DevSubBox) the ray misses
             // returns None (ray.rs:104-168 can only return a triangle the exact test accepts); dropping it from
@@ -415,6 +441,7 @@ __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const 
                 if (!cull_box(cr, s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, __int_as_float(0x7f800000), tn)) hitmask &= ~(1u << kk);
             }
 #endif
+            RRT_STAT(2, __popc(hitmask));
             if (hitmask) {
                 // stable sort by key (ray.rs:146-147) as repeated selection of the smallest remaining key,
                 // lowest child index first among equals; the last remaining child needs no comparison.
