@@ -213,6 +213,106 @@ __device__ __forceinline__ bool test_record(const V3& o, const V3& d, const DevT
 #endif
 #ifndef RRT_CULL_LOOP
 #define RRT_CULL_LOOP 0   // 0: if leaf / else inner per iteration; 1: inner step then leaf step; 2: descend-until-leaf
+                          // 3: EXPERIMENT (round 2 measures it) — leaves are queued while the hierarchy is walked and
+                          //    tested afterwards, so that the lanes of a warp meet in ONE exact-test block per list
+                          //    instead of one per loop iteration (profiles: Moller-Trumbore runs at 10-16 of 32 lanes).
+                          //    Records of a list may be tested in any order (test_record), and the f32 limit only ever
+                          //    prunes: testing later can only test more, never decide differently.
+#endif
+#ifndef RRT_PEND
+#define RRT_PEND 8        // RRT_CULL_LOOP == 3: queued leaves before the walk pauses to test them
+#endif
+
+#ifndef RRT_SLAB_PRED
+#define RRT_SLAB_PRED 0   // EXPERIMENT (round 2 measures it): which children the exact slabs hit, from pairwise comparisons
+                          // of the plane quotients instead of per-child tmin / tmax; sort keys only where two or more
+                          // children survive (tools/walk_stats.py: ~10 % of the visited nodes of c4, 6 % of c2)
+#endif
+
+#if RRT_SLAB_PRED
+// ray.rs:29-46 for one child box, reformulated.  With e_a / x_a the entry / exit quotient of the child's half on axis
+// a (mn / mx of slab_axis, never NaN: the slow path replaces a NaN pair by the identities of the chains):
+//     tmin = max(e_x, e_y, e_z),  tmax = min(x_x, x_y, x_z)
+//     !(tmax < 0)     <=>  x_x >= 0 and x_y >= 0 and x_z >= 0
+//     !(tmin > tmax)  <=>  e_a <= x_b for all nine (a, b)
+// and e_a <= x_a always holds (fast path: the quotients of an axis are monotone in the plane; slow path: fmin <= fmax
+// of the same pair, or -inf <= +inf for a replaced pair).  What is left are the six cross-axis comparisons and three
+// signs: per PAIR of axes and pair of halves one predicate chain `e_a <= x_b and e_b <= x_a and x_c >= 0` decides two
+// children at once (twelve chains, 36 DSETP, for what per-child min / max chains take ~100 instructions).
+__device__ __forceinline__ uint32_t slab_pair_bits(double e1, double x1, double e2, double x2, double s, uint32_t bits) {
+#if defined(__CUDA_ARCH__)
+    uint32_t r;
+    asm("{\n\t.reg .pred p;\n\tsetp.le.f64 p, %1, %2;\n\tsetp.le.and.f64 p, %3, %4, p;\n\t"
+        "setp.ge.and.f64 p, %5, 0d0000000000000000, p;\n\tselp.u32 %0, %6, 0, p;\n\t}"
+        : "=r"(r)
+        : "d"(e1), "d"(x1), "d"(e2), "d"(x2), "d"(s), "r"(bits));
+    return r;
+#else   // host build of this header (tests/host_emulation): the same predicate in C
+    return (e1 <= x1 && e2 <= x2 && s >= 0.0) ? bits : 0u;
+#endif
+}
+
+// child k: x half = k in {2,3,6,7}, y half = k >= 4, z half = k in {1,2,5,6} (octree.rs:216-225 order, as below)
+__device__ __forceinline__ uint32_t children_hit_pred(const double (&mnx)[2], const double (&mxx)[2], const double (&mny)[2],
+                                                      const double (&mxy)[2], const double (&mnz)[2], const double (&mxz)[2]) {
+    // (x half, y half): children {0,1} {2,3} {4,5} {6,7}; carries the sign of the x exit
+    const uint32_t xy = slab_pair_bits(mnx[0], mxy[0], mny[0], mxx[0], mxx[0], 0x03u) |
+                        slab_pair_bits(mnx[1], mxy[0], mny[0], mxx[1], mxx[1], 0x0Cu) |
+                        slab_pair_bits(mnx[0], mxy[1], mny[1], mxx[0], mxx[0], 0x30u) |
+                        slab_pair_bits(mnx[1], mxy[1], mny[1], mxx[1], mxx[1], 0xC0u);
+    // (x half, z half): children {0,4} {1,5} {3,7} {2,6}; carries the sign of the z exit
+    const uint32_t xz = slab_pair_bits(mnx[0], mxz[0], mnz[0], mxx[0], mxz[0], 0x11u) |
+                        slab_pair_bits(mnx[0], mxz[1], mnz[1], mxx[0], mxz[1], 0x22u) |
+                        slab_pair_bits(mnx[1], mxz[0], mnz[0], mxx[1], mxz[0], 0x88u) |
+                        slab_pair_bits(mnx[1], mxz[1], mnz[1], mxx[1], mxz[1], 0x44u);
+    // (y half, z half): children {0,3} {1,2} {4,7} {5,6}; carries the sign of the y exit
+    const uint32_t yz = slab_pair_bits(mny[0], mxz[0], mnz[0], mxy[0], mxy[0], 0x09u) |
+                        slab_pair_bits(mny[0], mxz[1], mnz[1], mxy[0], mxy[0], 0x06u) |
+                        slab_pair_bits(mny[1], mxz[0], mnz[0], mxy[1], mxy[1], 0x90u) |
+                        slab_pair_bits(mny[1], mxz[1], mnz[1], mxy[1], mxy[1], 0x60u);
+    return xy & xz & yz;
+}
+
+// Visiting order of two or more surviving children (ray.rs:146-147): their keys from the quotients, then the same
+// stable selection sort as the default path.  Cold: reached from ~10 % of the node visits, never inlined.
+static __device__ __noinline__ uint32_t children_order_keys(const double* __restrict__ planes, double ox, double dx, double yx,
+                                                            double oy, double dy, double yy, double oz, double dz, double yz_,
+                                                            uint32_t fastneg, uint32_t hitmask, uint32_t kept) {
+    AxisRay ax{ox, dx, yx, (fastneg & 1u) != 0u, (fastneg & 8u) != 0u}, ay{oy, dy, yy, (fastneg & 2u) != 0u, (fastneg & 16u) != 0u},
+        az{oz, dz, yz_, (fastneg & 4u) != 0u, (fastneg & 32u) != 0u};
+    double mnx[2], mxx[2], mny[2], mxy[2], mnz[2], mxz[2];
+    slab_axis(ax, __ldg(planes + 0), __ldg(planes + 1), __ldg(planes + 2), mnx[0], mnx[1], mxx[0], mxx[1]);
+    slab_axis(ay, __ldg(planes + 3), __ldg(planes + 4), __ldg(planes + 5), mny[0], mny[1], mxy[0], mxy[1]);
+    slab_axis(az, __ldg(planes + 6), __ldg(planes + 7), __ldg(planes + 8), mnz[0], mnz[1], mxz[0], mxz[1]);
+    double key[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const int xh = (k == 2 || k == 3 || k == 6 || k == 7) ? 1 : 0, yh = k >= 4 ? 1 : 0,
+                  zh = (k == 1 || k == 2 || k == 5 || k == 6) ? 1 : 0;
+        const double tmin = max_nn(max_nn(mnx[xh], mny[yh]), mnz[zh]);  // ray.rs:29-32
+        const double tmax = min_nn(min_nn(mxx[xh], mxy[yh]), mxz[zh]);  // ray.rs:33-36
+        key[k] = (tmin < 0.0) ? tmax : tmin;                             // ray.rs:49-53
+    }
+    uint32_t order = 0, rem = hitmask, shift = 0;
+    const uint32_t nh = __popc(hitmask);
+#pragma unroll 1
+    for (uint32_t r = 1; r < nh; ++r) {
+        double bk = 0.0;
+        uint32_t bi = 8;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const bool take = ((rem >> k) & 1u) && (bi == 8u || key[k] < bk);
+            bk = take ? key[k] : bk;
+            bi = take ? (uint32_t)k : bi;
+        }
+        rem &= ~(1u << bi);
+        order |= (uint32_t)__popc(kept & ((1u << bi) - 1u)) << shift;
+        shift += 3;
+    }
+    const uint32_t last = (uint32_t)__ffs(rem) - 1u;
+    order |= (uint32_t)__popc(kept & ((1u << last) - 1u)) << shift;
+    return order | (nh << 24);
+}
 #endif
 
 // Ray::intersect_with_octant_with_max_t(octree, 0, max_t).  any_hit: the caller only needs Some/None
@@ -291,8 +391,21 @@ __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const 
 #ifdef RRT_WALK_STATS
             unsigned ws_inner = 0, ws_leaf = 0, ws_first = 0;
 #endif
+#if RRT_CULL_LOOP == 3
+            uint32_t pend[RRT_PEND];
+            int np = 0;
+            for (;;) {
+              while (live && np < RRT_PEND) {
+                if (cur & kLeafBit) {
+                    pend[np++] = cur;
+                    if (csp != 0) cur = cstk[--csp];
+                    else live = false;
+                } else {
+#else
             while (live) {
-#if RRT_CULL_LOOP == 2
+#endif
+#if RRT_CULL_LOOP == 3
+#elif RRT_CULL_LOOP == 2
                 while (live && !(cur & kLeafBit)) {
 #elif RRT_CULL_LOOP == 1
                 if (!(cur & kLeafBit)) {
@@ -347,14 +460,23 @@ __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const 
                         live = false;
                     }
                 }
-#if RRT_CULL_LOOP == 0
+#if RRT_CULL_LOOP == 3
+              }
+              bool upd = false;
+#pragma unroll 1
+              for (int j = 0; j < np; ++j) {
+                    const uint32_t first = pend[j] & 0x0FFFFFFFu;
+                    const uint32_t cnt = ((pend[j] >> 28) & 7u) + 1u;
+#elif RRT_CULL_LOOP == 0
                 if (was_leaf) {
 #else
                 if (live && (cur & kLeafBit)) {
 #endif
+#if RRT_CULL_LOOP != 3
                     const uint32_t first = cur & 0x0FFFFFFFu;
                     const uint32_t cnt = ((cur >> 28) & 7u) + 1u;
                     bool upd = false;
+#endif
 #if RRT_LEAF_NOUNROLL
 #pragma unroll 1
 #endif
@@ -366,6 +488,15 @@ __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const 
                     ws_leaf++;
                     if (upd && !ws_first) ws_first = ws_inner + 1;   // inner steps before the first accepted record (+1)
 #endif
+#if RRT_CULL_LOOP == 3
+              }
+              np = 0;
+              if (!live || (any_hit && nb.id != kNone && nb.t < best.t)) break;  // list done / best will improve => Some
+#if RRT_CULL_F32
+              if (upd) limit = __double2float_ru(nb.t);
+#endif
+            }
+#else
                     if (any_hit && nb.id != kNone && nb.t < best.t) break;  // best will improve => Some
 #if RRT_CULL_F32
                     if (upd) limit = __double2float_ru(nb.t);
@@ -374,6 +505,7 @@ __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const 
                     else live = false;
                 }
             }
+#endif
             RRT_STAT(3, ws_inner);
             RRT_STAT(4, ws_leaf);
             RRT_STAT(5, ws_first);
@@ -399,6 +531,9 @@ __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const 
             slab_axis(ax, q0.x, q0.y, q1.x, mnx[0], mnx[1], mxx[0], mxx[1]);
             slab_axis(ay, q1.y, q2.x, q2.y, mny[0], mny[1], mxy[0], mxy[1]);
             slab_axis(az, q3.x, q3.y, q4, mnz[0], mnz[1], mxz[0], mxz[1]);
+#if RRT_SLAB_PRED
+            uint32_t hitmask = children_hit_pred(mnx, mxx, mny, mxy, mnz, mxz);
+#else
             // max(max(x, y), z) / min(min(x, y), z) of ray.rs:29-36: the (x, y) part is shared by the two
             // children that differ only in z
             double nxy[2][2], fxy[2][2];
@@ -420,6 +555,7 @@ __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const 
                 key[k] = (tmin < 0.0) ? tmax : tmin;                 // ray.rs:49-53
                 hitmask |= slab_hit_bit(tmin, tmax, 1u << k);        // ray.rs:39-46
             }
+#endif
             hitmask &= m.y;
             if (COUNT) tc.box += __popc(m.y);
             RRT_STAT(0, __popc(m.y));
@@ -442,6 +578,22 @@ __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const 
             }
 #endif
             RRT_STAT(2, __popc(hitmask));
+#if RRT_SLAB_PRED
+            if (hitmask) {
+                uint32_t ordw;
+                if (hitmask & (hitmask - 1u)) {   // two or more children left: their order needs the keys
+                    ordw = children_order_keys(&n->px[0], ax.o, ax.d, ax.y, ay.o, ay.d, ay.y, az.o, az.d, az.y,
+                                               (ax.fast ? 1u : 0u) | (ay.fast ? 2u : 0u) | (az.fast ? 4u : 0u) |
+                                                   (ax.neg ? 8u : 0u) | (ay.neg ? 16u : 0u) | (az.neg ? 32u : 0u),
+                                               hitmask, m.y);
+                } else {
+                    ordw = (uint32_t)__popc(m.y & (hitmask - 1u)) | (1u << 24);
+                }
+                if (lv_ord >> 24) stk[sp++] = make_uint2(lv_first, lv_ord);
+                lv_first = m.x;
+                lv_ord = ordw;
+            }
+#else
             if (hitmask) {
                 // stable sort by key (ray.rs:146-147) as repeated selection of the smallest remaining key,
                 // lowest child index first among equals; the last remaining child needs no comparison.
@@ -469,6 +621,7 @@ __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const 
                 lv_first = m.x;
                 lv_ord = order | (nh << 24);
             }
+#endif
         }
 
 #if RRT_CULL_F32 && RRT_SUB_BOX == 1

@@ -18,7 +18,10 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 EMU_DIR = os.path.join(HERE, "host_emulation")
 EMU_SRC = os.path.join(EMU_DIR, "emu_trace.cpp")
-EMU_LIB = os.path.join(EMU_DIR, "libemu_trace.so")
+# RRT_EMU_FLAGS="-DRRT_SLAB_PRED=1 ...": the same tests over a compile-time VARIANT of the traversal headers (the flags a
+# variant build of the library gets through RRT_EXTRA_FLAGS), in its own library file
+EMU_FLAGS = os.environ.get("RRT_EMU_FLAGS", "").split()
+EMU_LIB = os.path.join(EMU_DIR, "libemu_trace" + "".join(c if c.isalnum() else "_" for c in "".join(EMU_FLAGS)) + ".so")
 CSRC = os.path.join(ROOT, "rust-ray-tracer_b200", "csrc")
 
 
@@ -27,7 +30,7 @@ def _build_emu():
         os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h", ".cpp"))]
     if os.path.exists(EMU_LIB) and all(os.path.getmtime(EMU_LIB) >= os.path.getmtime(d) for d in deps):
         return
-    flags = ["-O2", "-std=c++17", "-ffp-contract=off", "-fno-fast-math", "-fopenmp", "-fPIC", "-shared", "-w"]
+    flags = ["-O2", "-std=c++17", "-ffp-contract=off", "-fno-fast-math", "-fopenmp", "-fPIC", "-shared", "-w"] + EMU_FLAGS
     try:
         if " fma " in open("/proc/cpuinfo").read():
             flags.append("-mfma")          # hardware single-rounding fma(); without it glibc's exact software fma is used

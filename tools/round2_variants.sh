@@ -1,0 +1,22 @@
+#!/bin/bash
+# Builds the compile-time variants prepared at the end of round 1 (no GPU was left to time them) into variants/
+# (git-ignored, travels with gpurun).  Every variant passes the host-emulation suite bit for bit:
+#     RRT_EMU_FLAGS="<flags>" python -m pytest tests/test_host_emulation.py -q
+# Build here, then on a GPU box:
+#     gpurun --timeout 900 -- 'python tools/variant_sweep.py variants/*.so -- c2 c4 c5 > gpurun_out/variants.txt 2>&1'
+# (variant_sweep.py checks that every variant renders the same frame and hit-id plane, sha1, and prints its time).
+set -e
+cd "$(dirname "$0")/.."
+mkdir -p variants
+build() {   # name flags...
+  local name=$1; shift
+  RRT_OUT=$PWD/variants/$name.so RRT_EXTRA_FLAGS="$*" python rust-ray-tracer_b200/build.py --force > /dev/null 2>&1
+  printf "%-14s %-55s %s\n" "$name" "$*" "$(python tools/sass_count.py variants/$name.so --kernel render_kernelILb0ELb1 | grep -o '[0-9]* instructions')"
+}
+build a_default
+build b_pred        -DRRT_SLAB_PRED=1
+build c_l3p1        -DRRT_CULL_LOOP=3 -DRRT_PEND=1
+build d_l3p2        -DRRT_CULL_LOOP=3 -DRRT_PEND=2
+build e_l3p3        -DRRT_CULL_LOOP=3 -DRRT_PEND=3
+build f_l3p4        -DRRT_CULL_LOOP=3 -DRRT_PEND=4
+build g_pred_l3p2   -DRRT_SLAB_PRED=1 -DRRT_CULL_LOOP=3 -DRRT_PEND=2
