@@ -225,8 +225,8 @@ __device__ __forceinline__ bool test_record(const V3& o, const V3& d, const DevT
 
 #ifndef RRT_SLAB_PRED
 #define RRT_SLAB_PRED 0   // EXPERIMENT (round 2 measures it): which children the exact slabs hit, from pairwise comparisons
-                          // of the plane quotients instead of per-child tmin / tmax; sort keys only where two or more
-                          // children survive (tools/walk_stats.py: ~10 % of the visited nodes of c4, 6 % of c2)
+                          // of the plane quotients instead of per-child tmin / tmax; tmin / tmax / sort keys only where
+                          // two or more children are hit (tools/walk_stats.py: 27 % of the node visits of c4, 33 % of c2)
 #endif
 
 #if RRT_SLAB_PRED
@@ -273,46 +273,6 @@ __device__ __forceinline__ uint32_t children_hit_pred(const double (&mnx)[2], co
     return xy & xz & yz;
 }
 
-// Visiting order of two or more surviving children (ray.rs:146-147): their keys from the quotients, then the same
-// stable selection sort as the default path.  Cold: reached from ~10 % of the node visits, never inlined.
-static __device__ __noinline__ uint32_t children_order_keys(const double* __restrict__ planes, double ox, double dx, double yx,
-                                                            double oy, double dy, double yy, double oz, double dz, double yz_,
-                                                            uint32_t fastneg, uint32_t hitmask, uint32_t kept) {
-    AxisRay ax{ox, dx, yx, (fastneg & 1u) != 0u, (fastneg & 8u) != 0u}, ay{oy, dy, yy, (fastneg & 2u) != 0u, (fastneg & 16u) != 0u},
-        az{oz, dz, yz_, (fastneg & 4u) != 0u, (fastneg & 32u) != 0u};
-    double mnx[2], mxx[2], mny[2], mxy[2], mnz[2], mxz[2];
-    slab_axis(ax, __ldg(planes + 0), __ldg(planes + 1), __ldg(planes + 2), mnx[0], mnx[1], mxx[0], mxx[1]);
-    slab_axis(ay, __ldg(planes + 3), __ldg(planes + 4), __ldg(planes + 5), mny[0], mny[1], mxy[0], mxy[1]);
-    slab_axis(az, __ldg(planes + 6), __ldg(planes + 7), __ldg(planes + 8), mnz[0], mnz[1], mxz[0], mxz[1]);
-    double key[8];
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-        const int xh = (k == 2 || k == 3 || k == 6 || k == 7) ? 1 : 0, yh = k >= 4 ? 1 : 0,
-                  zh = (k == 1 || k == 2 || k == 5 || k == 6) ? 1 : 0;
-        const double tmin = max_nn(max_nn(mnx[xh], mny[yh]), mnz[zh]);  // ray.rs:29-32
-        const double tmax = min_nn(min_nn(mxx[xh], mxy[yh]), mxz[zh]);  // ray.rs:33-36
-        key[k] = (tmin < 0.0) ? tmax : tmin;                             // ray.rs:49-53
-    }
-    uint32_t order = 0, rem = hitmask, shift = 0;
-    const uint32_t nh = __popc(hitmask);
-#pragma unroll 1
-    for (uint32_t r = 1; r < nh; ++r) {
-        double bk = 0.0;
-        uint32_t bi = 8;
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            const bool take = ((rem >> k) & 1u) && (bi == 8u || key[k] < bk);
-            bk = take ? key[k] : bk;
-            bi = take ? (uint32_t)k : bi;
-        }
-        rem &= ~(1u << bi);
-        order |= (uint32_t)__popc(kept & ((1u << bi) - 1u)) << shift;
-        shift += 3;
-    }
-    const uint32_t last = (uint32_t)__ffs(rem) - 1u;
-    order |= (uint32_t)__popc(kept & ((1u << last) - 1u)) << shift;
-    return order | (nh << 24);
-}
 #endif
 
 // Ray::intersect_with_octant_with_max_t(octree, 0, max_t).  any_hit: the caller only needs Some/None
@@ -532,7 +492,18 @@ __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const 
             slab_axis(ay, q1.y, q2.x, q2.y, mny[0], mny[1], mxy[0], mxy[1]);
             slab_axis(az, q3.x, q3.y, q4, mnz[0], mnz[1], mxz[0], mxz[1]);
 #if RRT_SLAB_PRED
-            uint32_t hitmask = children_hit_pred(mnx, mxx, mny, mxy, mnz, mxz);
+            uint32_t hitmask = children_hit_pred(mnx, mxx, mny, mxy, mnz, mxz) & m.y;
+            double key[8];
+            if (hitmask & (hitmask - 1u)) {   // two or more children hit: the sort below may need their keys
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    const int xh = (k == 2 || k == 3 || k == 6 || k == 7) ? 1 : 0, yh = k >= 4 ? 1 : 0,
+                              zh = (k == 1 || k == 2 || k == 5 || k == 6) ? 1 : 0;
+                    const double tmin = max_nn(max_nn(mnx[xh], mny[yh]), mnz[zh]);  // ray.rs:29-32
+                    const double tmax = min_nn(min_nn(mxx[xh], mxy[yh]), mxz[zh]);  // ray.rs:33-36
+                    key[k] = (tmin < 0.0) ? tmax : tmin;                             // ray.rs:49-53
+                }
+            }
 #else
             // max(max(x, y), z) / min(min(x, y), z) of ray.rs:29-36: the (x, y) part is shared by the two
             // children that differ only in z
@@ -578,22 +549,6 @@ __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const 
             }
 #endif
             RRT_STAT(2, __popc(hitmask));
-#if RRT_SLAB_PRED
-            if (hitmask) {
-                uint32_t ordw;
-                if (hitmask & (hitmask - 1u)) {   // two or more children left: their order needs the keys
-                    ordw = children_order_keys(&n->px[0], ax.o, ax.d, ax.y, ay.o, ay.d, ay.y, az.o, az.d, az.y,
-                                               (ax.fast ? 1u : 0u) | (ay.fast ? 2u : 0u) | (az.fast ? 4u : 0u) |
-                                                   (ax.neg ? 8u : 0u) | (ay.neg ? 16u : 0u) | (az.neg ? 32u : 0u),
-                                               hitmask, m.y);
-                } else {
-                    ordw = (uint32_t)__popc(m.y & (hitmask - 1u)) | (1u << 24);
-                }
-                if (lv_ord >> 24) stk[sp++] = make_uint2(lv_first, lv_ord);
-                lv_first = m.x;
-                lv_ord = ordw;
-            }
-#else
             if (hitmask) {
                 // stable sort by key (ray.rs:146-147) as repeated selection of the smallest remaining key,
                 // lowest child index first among equals; the last remaining child needs no comparison.
@@ -621,7 +576,6 @@ __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const 
                 lv_first = m.x;
                 lv_ord = order | (nh << 24);
             }
-#endif
         }
 
 #if RRT_CULL_F32 && RRT_SUB_BOX == 1
