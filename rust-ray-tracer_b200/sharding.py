@@ -154,3 +154,74 @@ def gather_frame_cpu(local_rows, width, height, tile_rows, rank, world, group=No
     dist.all_gather(out, mine, group=group)
     g = np.stack([o.numpy().view(np.uint32) for o in out])
     return deinterleave_host(g, width, height, tile_rows, world)
+
+
+# ---------------------------------------------------------------- frame-parallel sequences (SURVEY §8e "Orbit", §8 f4)
+# The frames of an animation are as independent as the pixels of a frame (the scene is immutable, only the camera
+# moves): frame k of a sequence belongs to rank k % world, each rank renders WHOLE frames with the multi-frame call
+# (rrt_render_frames: frame i leaves for the host while frame i+1 renders) and nothing is exchanged until the
+# sequence is collected.  No per-frame gather, no per-frame drain tail; the price is latency (a frame is as slow as
+# one GPU makes it), so this is the mode for offline sequences such as config 5's 64-frame orbit, tile rows the mode
+# for one frame as fast as possible.
+
+def owned_frames(n_frames, world, rank):
+    """Indices (ascending) of the frames `rank` renders: k % world == rank."""
+    return list(range(rank, n_frames, world))
+
+
+def gather_frames(local, n_frames, rank, world, dst=0, group=None, device=None):
+    """Collect a frame-parallel sequence on rank `dst`: local = (len(owned_frames), H, W) u32 numpy array of this
+    rank's frames in ascending frame order -> (n_frames, H, W) on dst, None elsewhere.  One gather of equally sized
+    (padded) blocks; NCCL needs device tensors (`device`), gloo takes the host arrays as they are."""
+    import torch
+    import torch.distributed as dist
+    mine = owned_frames(n_frames, world, rank)
+    if local.dtype != np.uint32 or local.ndim != 3 or local.shape[0] != len(mine):
+        raise ValueError("local must be (len(owned_frames), H, W) uint32")
+    H, W = local.shape[1:]
+    per = (n_frames + world - 1) // world            # rank 0 owns the most
+    pad = np.zeros((per, H, W), dtype=np.uint32)
+    pad[:len(mine)] = local
+    t = torch.from_numpy(pad.view(np.int32))
+    if device is not None:
+        t = t.to(device)
+    if world == 1:
+        blocks = [t]
+    else:
+        blocks = [torch.empty_like(t) for _ in range(world)] if rank == dst else None
+        dist.gather(t, blocks, dst=dst, group=group)
+    if rank != dst:
+        return None
+    out = np.zeros((n_frames, H, W), dtype=np.uint32)
+    for r in range(world):
+        fr = owned_frames(n_frames, world, r)
+        out[fr] = blocks[r].cpu().numpy().view(np.uint32)[:len(fr)]
+    return out
+
+
+class FrameParallelSequence:
+    """One process per GPU, scene replicated (as ShardedRenderer): render_local() renders this rank's frames of a
+    sequence through Scene.draw_frames, collect() gathers the sequence on one rank."""
+
+    def __init__(self, ray_tracer, width, height, rank, world, group=None):
+        self.rt, self.W, self.H = ray_tracer, width, height
+        self.rank, self.world, self.group = rank, world, group
+        self.device_ms = None
+
+    def render_local(self, overrides_per_frame, out=None):
+        """overrides_per_frame: the WHOLE sequence (every rank passes the same list); -> this rank's frames,
+        (len(owned_frames), H, W) u32, frame owned_frames(...)[i] at [i]."""
+        from .scene import Scene
+        mine = owned_frames(len(overrides_per_frame), self.world, self.rank)
+        sc = Scene(self.W, self.H)
+        frames = sc.draw_frames(self.rt, [overrides_per_frame[k] for k in mine], out=out)
+        self.device_ms = sc.device_ms
+        return frames
+
+    def collect(self, local, n_frames, dst=0):
+        import torch
+        import torch.distributed as dist
+        device = None
+        if self.world > 1 and dist.get_backend(self.group) == "nccl":
+            device = torch.device("cuda", self.rt.device)
+        return gather_frames(local, n_frames, self.rank, self.world, dst=dst, group=self.group, device=device)

@@ -259,3 +259,23 @@ def test_render_frames_equals_single_frames(rrt, scenes):
         assert np.array_equal(seq[i], s) and np.array_equal(seq_pinned[i], s)
     assert rrt.Scene(W, H).draw_frames(rt, []).shape == (0, H, W)
     rt.close()
+
+
+def test_frame_parallel_sequence_world1(rrt, scenes):
+    # frame-parallel sequences (sharding.FrameParallelSequence): with one rank the sequence is what draw_frames gives;
+    # the N>1 assignment / gather is covered on CPU (tests/test_sharding_gloo.py)
+    from rrt_b200.sharding import FrameParallelSequence
+    sd = scenes("model2")
+    rt = rrt.RayTracer(sd)
+    W, H = 320, 180
+    cams = []
+    for k in (0, 9, 31):
+        origin, rot = rrt.orbit_camera(k)
+        cams.append(dict(origin=origin, camera_rot=rot))
+    fps = FrameParallelSequence(rt, W, H, rank=0, world=1)
+    local = fps.render_local(cams)
+    seq = fps.collect(local, len(cams))
+    sc = rrt.Scene(W, H)
+    for i, c in enumerate(cams):
+        assert np.array_equal(seq[i], sc.draw_scene(rt, **c))
+    rt.close()

@@ -70,3 +70,54 @@ def test_deinterleave_host_matches_shard_mapping():
     e = _pattern(range(H), W)
     e[0] = 0
     assert np.array_equal(deinterleave_host(g, W, H, T, G), e)
+
+
+# ---------------------------------------------------------------- frame-parallel sequences
+def _frame_pattern(k, W, H):
+    return (_pattern(range(H), W) + np.uint32(k * 65537)) & 0x00FFFFFF
+
+
+def _seq_worker(rank, world, port, n, W, H, q):
+    sys.path.insert(0, ROOT)
+    import torch.distributed as dist
+    import rrt_b200  # noqa: F401
+    from rrt_b200.sharding import gather_frames, owned_frames
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    mine = owned_frames(n, world, rank)
+    local = np.stack([_frame_pattern(k, W, H) for k in mine]) if mine else np.zeros((0, H, W), np.uint32)
+    seq = gather_frames(local, n, rank, world, dst=0)
+    ok = seq is None if rank != 0 else all(np.array_equal(seq[k], _frame_pattern(k, W, H)) for k in range(n)) and seq.shape == (n, H, W)
+    q.put((rank, bool(ok), len(mine)))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,n", [(2, 5), (3, 7), (3, 2)])
+def test_gloo_frame_parallel_sequence(world, n):
+    # frame k is rendered by rank k % world; one gather of padded blocks puts the sequence together on rank 0 —
+    # ragged shares (n not a multiple of world) and a rank without any frame included
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    ps = [ctx.Process(target=_seq_worker, args=(r, world, port, n, 24, 10, q)) for r in range(world)]
+    for p in ps:
+        p.start()
+    res = [q.get(timeout=120) for _ in range(world)]
+    for p in ps:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert all(ok for _, ok, _ in res)
+    assert sum(m for _, _, m in res) == n
+
+
+def test_owned_frames_partition():
+    sys.path.insert(0, ROOT)
+    import rrt_b200  # noqa: F401
+    from rrt_b200.sharding import gather_frames, owned_frames
+    for world in (1, 2, 3, 8):
+        for n in (0, 1, 7, 64):
+            parts = [owned_frames(n, world, r) for r in range(world)]
+            assert sorted(k for p in parts for k in p) == list(range(n))
+            assert max(len(p) for p in parts) - min(len(p) for p in parts) <= 1
+    one = np.stack([_frame_pattern(k, 6, 4) for k in range(3)])
+    assert np.array_equal(gather_frames(one, 3, 0, 1), one)       # world 1: no process group needed
