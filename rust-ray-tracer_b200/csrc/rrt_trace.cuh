@@ -219,6 +219,15 @@ __device__ __forceinline__ bool test_record(const V3& o, const V3& d, const DevT
                           //    Records of a list may be tested in any order (test_record), and the f32 limit only ever
                           //    prunes: testing later can only test more, never decide differently.
 #endif
+#ifndef RRT_LATE_PRUNE
+#define RRT_LATE_PRUNE 0  // EXPERIMENT (round 2 measures it): once nothing is pending at any level (no unvisited sibling of
+                          // the current node or of an ancestor: the state after a node accepted an own triangle, and along
+                          // every single-child chain below it), the rest of the walk can only matter by IMPROVING `best` —
+                          // there is no sibling left for a `Some` to cut off (ray.rs:155-160).  Then (a) the node's own list
+                          // is searched with limit min(nb.t, best.t) from the start, and (b) the trailing children of the
+                          // sorted order whose subtree boxes begin beyond best.t are not visited (a SUFFIX only: a dropped
+                          // child could otherwise have returned Some and cut off a later sibling).
+#endif
 #ifndef RRT_PEND
 #define RRT_PEND 8        // RRT_CULL_LOOP == 3: queued leaves before the walk pauses to test them
 #endif
@@ -330,7 +339,13 @@ __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const 
         nb.rec = 0;
         nb.t = is_root ? max_t : kInf;
 #if RRT_CULL_F32
+#if RRT_LATE_PRUNE
+        // nothing pending anywhere: own records at t >= best.t can neither improve `best` nor cut anything off
+        const bool alone = sp == 0 && (lv_ord >> 24) == 0u;
+        float limit = __double2float_ru(alone ? min_nn(nb.t, best.t) : nb.t);
+#else
         float limit = __double2float_ru(nb.t);
+#endif
         bool scan = m.w != 0u;
 #if RRT_LIST_BOX
         if (scan) {  // the node's own list as a whole
@@ -453,13 +468,17 @@ __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const 
               np = 0;
               if (!live || (any_hit && nb.id != kNone && nb.t < best.t)) break;  // list done / best will improve => Some
 #if RRT_CULL_F32
-              if (upd) limit = __double2float_ru(nb.t);
+              if (upd) limit = fminf(limit, __double2float_ru(nb.t));
 #endif
             }
 #else
                     if (any_hit && nb.id != kNone && nb.t < best.t) break;  // best will improve => Some
 #if RRT_CULL_F32
+#if RRT_LATE_PRUNE
+                    if (upd) limit = fminf(limit, __double2float_ru(nb.t));
+#else
                     if (upd) limit = __double2float_ru(nb.t);
+#endif
 #endif
                     if (csp != 0) cur = cstk[--csp];
                     else live = false;
@@ -537,15 +556,27 @@ __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const 
             // the sorted list is invisible (stable sort; None children are skipped by the loop at ray.rs:152-161).
             // Tested here, for the children the exact slabs hit, rather than on entry: no sort slot, no push/pop,
             // and the box loads of one node are independent of each other.
+#if RRT_LATE_PRUNE
+            // after this node's own list: is anything pending besides the children about to be pushed?
+            const bool alone_c = sp == 0 && (lv_ord >> 24) == 0u;
+            const float far_limit = alone_c ? __double2float_ru(best.t) : __int_as_float(0x7f800000);
+            uint32_t far_r = 0;   // by rank among the kept children: subtree box begins beyond best.t
+#endif
             for (uint32_t left = hitmask; left;) {
                 const uint32_t kk = (uint32_t)__ffs(left) - 1u;
                 left &= left - 1u;
-                const float4* sb = reinterpret_cast<const float4*>(sc.sub_boxes + (m.x + (uint32_t)__popc(m.y & ((1u << kk) - 1u))));
+                const uint32_t rank = (uint32_t)__popc(m.y & ((1u << kk) - 1u));
+                const float4* sb = reinterpret_cast<const float4*>(sc.sub_boxes + (m.x + rank));
                 const float4 s0 = __ldg(sb);
                 const float2 s1 = __ldg(reinterpret_cast<const float2*>(sb + 1));
                 float tn;
                 if (COUNT) tc.cull++;
                 if (!cull_box(cr, s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, __int_as_float(0x7f800000), tn)) hitmask &= ~(1u << kk);
+#if RRT_LATE_PRUNE
+                // same proof as cull_box's limit: every acceptable t* in the box has t* >= tn, so tn > ru(best.t) means
+                // t* > best.t — this subtree cannot improve `best` (strict '<', ray.rs:163)
+                else if (cr.ok && tn > far_limit) far_r |= 1u << rank;
+#endif
             }
 #endif
             RRT_STAT(2, __popc(hitmask));
@@ -572,9 +603,19 @@ __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const 
                 }
                 const uint32_t last = (uint32_t)__ffs(rem) - 1u;
                 order |= (uint32_t)__popc(m.y & ((1u << last) - 1u)) << shift;
+#if RRT_LATE_PRUNE
+                uint32_t keep = nh;   // drop the trailing children that cannot improve `best` (alone_c only: far_r == 0 otherwise)
+                while (keep != 0u && ((far_r >> ((order >> (3u * (keep - 1u))) & 7u)) & 1u)) --keep;
+                if (keep != 0u) {
+                    if (lv_ord >> 24) stk[sp++] = make_uint2(lv_first, lv_ord);
+                    lv_first = m.x;
+                    lv_ord = (order & ((1u << (3u * keep)) - 1u)) | (keep << 24);
+                }
+#else
                 if (lv_ord >> 24) stk[sp++] = make_uint2(lv_first, lv_ord);
                 lv_first = m.x;
                 lv_ord = order | (nh << 24);
+#endif
             }
         }
 

@@ -20,3 +20,6 @@ build d_l3p2        -DRRT_CULL_LOOP=3 -DRRT_PEND=2
 build e_l3p3        -DRRT_CULL_LOOP=3 -DRRT_PEND=3
 build f_l3p4        -DRRT_CULL_LOOP=3 -DRRT_PEND=4
 build g_pred_l3p2   -DRRT_SLAB_PRED=1 -DRRT_CULL_LOOP=3 -DRRT_PEND=2
+build h_late        -DRRT_LATE_PRUNE=1
+build i_pred_late   -DRRT_SLAB_PRED=1 -DRRT_LATE_PRUNE=1
+build j_all         -DRRT_SLAB_PRED=1 -DRRT_LATE_PRUNE=1 -DRRT_CULL_LOOP=3 -DRRT_PEND=2

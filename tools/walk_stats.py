@@ -24,7 +24,7 @@ KINDS = ["children kept (child_mask)", "children the exact slabs hit", "children
 
 
 def build():
-    flags = ["-O2", "-std=c++17", "-ffp-contract=off", "-fno-fast-math", "-fopenmp", "-fPIC", "-shared", "-w", "-DRRT_WALK_STATS"]
+    flags = ["-O2", "-std=c++17", "-ffp-contract=off", "-fno-fast-math", "-fopenmp", "-fPIC", "-shared", "-w", "-DRRT_WALK_STATS"] + T.EMU_FLAGS
     if " fma " in open("/proc/cpuinfo").read():
         flags.append("-mfma")
     cuda_inc = os.path.join(os.environ.get("CUDA_HOME", "/usr/local/cuda"), "include")
@@ -58,7 +58,12 @@ def main():
         es.render_shard(p, want_hit_ids=False)
         hist = np.zeros((8, 64), dtype=np.uint64)
         L.walk_stats_get(hist.ctypes.data)
-        print(f"== {name}: {desc}, emulated at {w}x{h} ({4 * w * h} primary rays)")
+        print(f"== {name}: {desc}, emulated at {w}x{h} ({4 * w * h} primary rays), flags {' '.join(T.EMU_FLAGS) or '-'}")
+        ar = np.arange(64, dtype=float)
+        nray = 4.0 * w * h
+        print(f"  totals per primary ray (with its shadow / mirror rays): node visits {hist[6].sum() / nray:.2f}, with children "
+              f"{hist[0].sum() / nray:.2f}, subtree-box tests {(hist[1] * ar).sum() / nray:.2f}, own-list walks {hist[3].sum() / nray:.2f}, "
+              f"inner culling steps {(hist[3] * ar).sum() / nray:.2f}, exact-test steps {(hist[4] * ar).sum() / nray:.2f}")
         for k, label in enumerate(KINDS):
             row = hist[k].astype(float)
             tot = row.sum()
