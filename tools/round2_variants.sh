@@ -23,3 +23,5 @@ build g_pred_l3p2   -DRRT_SLAB_PRED=1 -DRRT_CULL_LOOP=3 -DRRT_PEND=2
 build h_late        -DRRT_LATE_PRUNE=1
 build i_pred_late   -DRRT_SLAB_PRED=1 -DRRT_LATE_PRUNE=1
 build j_all         -DRRT_SLAB_PRED=1 -DRRT_LATE_PRUNE=1 -DRRT_CULL_LOOP=3 -DRRT_PEND=2
+build k_all_mb7     -DRRT_SLAB_PRED=1 -DRRT_LATE_PRUNE=1 -DRRT_CULL_LOOP=3 -DRRT_PEND=2 -DRRT_MIN_BLOCKS=7
+build l_all_mb6     -DRRT_SLAB_PRED=1 -DRRT_LATE_PRUNE=1 -DRRT_CULL_LOOP=3 -DRRT_PEND=2 -DRRT_MIN_BLOCKS=6
