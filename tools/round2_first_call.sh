@@ -1,0 +1,13 @@
+#!/bin/bash
+# First GPU call of round 2 (everything written after round 1's GPU budget ended, in one go):
+#   here  :  bash tools/round2_variants.sh            (builds variants/*.so, ~6 min of CPU)
+#   then  :  gpurun --timeout 1500 -- 'bash tools/round2_first_call.sh'
+# 1. the GPU test suite incl. the two tests never run on a GPU (rrt_render_frames, frame-parallel world 1) and smoke()
+# 2. every prepared kernel variant on c2 / c3a / c4 / c5: time + sha1 of frame and hit-id plane (must equal a_default's)
+# 3. the default bench line (c4), so that the variant times have this box's baseline next to them
+o=gpurun_out
+python -m pytest tests -m gpu -x -q > $o/r02_pytest.log 2>&1; echo "pytest rc $? : $(tail -1 $o/r02_pytest.log)"
+python __graft_entry__.py smoke > $o/r02_smoke.log 2>&1; echo "smoke rc $? : $(tail -1 $o/r02_smoke.log)"
+python tools/variant_sweep.py variants/*.so -- c2 c3a c4 c5 > $o/r02_variants.txt 2>&1; echo "variants rc $?"
+grep -E "^==|ms" $o/r02_variants.txt | tail -80
+python bench.py > $o/r02_bench_c4_default.json 2> $o/r02_bench_c4_default.err; echo "bench rc $?"
