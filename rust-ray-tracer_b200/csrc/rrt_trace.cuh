@@ -284,6 +284,93 @@ __device__ __forceinline__ uint32_t children_hit_pred(const double (&mnx)[2], co
 
 #endif
 
+#ifndef RRT_SHADOW_FILTER
+#define RRT_SHADOW_FILTER 0   // EXPERIMENT (CPU work counters only so far): shadow queries first ask "is there ANY accepted
+                              // triangle with t < max_t in the conservative f32 hull of the walk?" — no f64 slabs, no sort,
+                              // any order.  None => the reference returns None (it can only return an accepted triangle
+                              // with t < max_t, ray.rs:163 at the root); otherwise the exact walk decides as before.
+#endif
+#if RRT_SHADOW_FILTER && RRT_CULL_F32
+// true: provably no triangle of the scene is accepted by the exact test with t < max_t.  Visits a SUPERSET of the nodes
+// the reference can reach (subtree boxes instead of exact child slabs), so a `true` is exact; `false` decides nothing.
+template <bool COUNT>
+__device__ __forceinline__ bool shadow_clear(const DevScene& sc, const V3& o, const V3& d, const double max_t, const CullRay& cr,
+                                             uint2* __restrict__ fstk, uint32_t* __restrict__ cstk, TraceCount& tc) {
+    // fstk / cstk: the walk's own stacks (it starts after this returns); fstk holds per open level the first child
+    // and the mask of the kept children still to visit
+    if (!cr.ok) return false;
+    const float limit = __double2float_ru(max_t);
+    int sp = 0;
+    uint32_t node = 0;
+    for (;;) {
+        const DevNode* __restrict__ n = sc.nodes + node;
+        const uint4 m = __ldg(reinterpret_cast<const uint4*>(&n->first_child));
+        if (COUNT) tc.nodes++;
+        RRT_STAT(7, 0);
+        bool scan = m.w != 0u;
+        if (scan) {
+            const float4 lb = __ldg(reinterpret_cast<const float4*>(&n->list_box[0]));
+            const float2 lc = __ldg(reinterpret_cast<const float2*>(&n->list_box[4]));
+            float tn;
+            if (COUNT) tc.cull++;
+            RRT_STAT(7, 1);
+            scan = cull_box(cr, lb.x, lb.y, lb.z, lb.w, lc.x, lc.y, limit, tn);
+        }
+        if (scan) {
+            uint32_t cur = __ldg(&n->cull_root);
+            int csp = 0;
+            for (;;) {
+                if (cur & kLeafBit) {
+                    const uint32_t first = cur & 0x0FFFFFFFu, cnt = ((cur >> 28) & 7u) + 1u;
+#pragma unroll 1
+                    for (uint32_t i = 0; i < cnt; ++i) {
+                        double t, u, v;
+                        uint32_t id;
+                        if (COUNT) tc.mt++;
+                        RRT_STAT(7, 2);
+                        if (moller_trumbore(o, d, sc.tris + first + i, t, u, v, id) && t < max_t) { RRT_STAT(7, 4); return false; }
+                    }
+                    if (csp == 0) break;
+                    cur = cstk[--csp];
+                } else {
+                    const DevCull* __restrict__ c = sc.cull + cur;
+                    const float4* bp = reinterpret_cast<const float4*>(c);
+                    const float4 f0 = __ldg(bp), f1 = __ldg(bp + 1), f2 = __ldg(bp + 2);
+                    const uint2 ch = __ldg(reinterpret_cast<const uint2*>(&c->child[0]));
+                    float tn0, tn1;
+                    if (COUNT) tc.cull += 2;
+                    RRT_STAT(7, 5);
+                    const bool go0 = cull_box(cr, f0.x, f0.y, f0.z, f0.w, f1.x, f1.y, limit, tn0);
+                    const bool go1 = cull_box(cr, f1.z, f1.w, f2.x, f2.y, f2.z, f2.w, limit, tn1);
+                    if (go0 && go1) { cstk[csp++] = ch.y; cur = ch.x; }
+                    else if (go0 || go1) cur = go0 ? ch.x : ch.y;
+                    else if (csp != 0) cur = cstk[--csp];
+                    else break;
+                }
+            }
+        }
+        // children: every kept child whose subtree box the segment [0, max_t] may touch
+        uint32_t todo = 0;
+        for (uint32_t left = m.y, rank = 0; left; left &= left - 1u, ++rank) {
+            const float4* sb = reinterpret_cast<const float4*>(sc.sub_boxes + (m.x + rank));
+            const float4 s0 = __ldg(sb);
+            const float2 s1 = __ldg(reinterpret_cast<const float2*>(sb + 1));
+            float tn;
+            if (COUNT) tc.cull++;
+            RRT_STAT(7, 6);
+            if (cull_box(cr, s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, limit, tn)) todo |= 1u << rank;
+        }
+        if (todo) fstk[sp++] = make_uint2(m.x, todo);
+        if (sp == 0) { RRT_STAT(7, 3); return true; }
+        uint2& top = fstk[sp - 1];
+        const uint32_t r = (uint32_t)__ffs(top.y) - 1u;
+        node = top.x + r;
+        top.y &= top.y - 1u;
+        if (top.y == 0u) --sp;
+    }
+}
+#endif
+
 // Ray::intersect_with_octant_with_max_t(octree, 0, max_t).  any_hit: the caller only needs Some/None
 // (shadow rays, raytracer.rs:181-187) — `best` only ever improves, so the first update decides.
 template <bool COUNT>
@@ -308,6 +395,9 @@ __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const 
     const double kInf = __longlong_as_double(0x7FF0000000000000ll);
 #if RRT_CULL_F32
     const CullRay cr = make_cull_ray(sc, o, d, ax, ay, az);
+#if RRT_SHADOW_FILTER
+    if (any_hit && shadow_clear<COUNT>(sc, o, d, max_t, cr, stk, cstk, tc)) return;   // best.id == kNone: None
+#endif
 #else
     // reciprocal direction for the CONSERVATIVE culling boxes only (never for a reference decision)
     const double ivx = min_nn(max_nn(ax.y, -1e300), 1e300), ivy = min_nn(max_nn(ay.y, -1e300), 1e300),

@@ -25,3 +25,6 @@ build i_pred_late   -DRRT_SLAB_PRED=1 -DRRT_LATE_PRUNE=1
 build j_all         -DRRT_SLAB_PRED=1 -DRRT_LATE_PRUNE=1 -DRRT_CULL_LOOP=3 -DRRT_PEND=2
 build k_all_mb7     -DRRT_SLAB_PRED=1 -DRRT_LATE_PRUNE=1 -DRRT_CULL_LOOP=3 -DRRT_PEND=2 -DRRT_MIN_BLOCKS=7
 build l_all_mb6     -DRRT_SLAB_PRED=1 -DRRT_LATE_PRUNE=1 -DRRT_CULL_LOOP=3 -DRRT_PEND=2 -DRRT_MIN_BLOCKS=6
+build m_filter      -DRRT_SHADOW_FILTER=1
+build n_filter_pred -DRRT_SHADOW_FILTER=1 -DRRT_SLAB_PRED=1
+build o_filter_all  -DRRT_SHADOW_FILTER=1 -DRRT_SLAB_PRED=1 -DRRT_LATE_PRUNE=1 -DRRT_CULL_LOOP=3 -DRRT_PEND=2

@@ -64,6 +64,10 @@ def main():
         print(f"  totals per primary ray (with its shadow / mirror rays): node visits {hist[6].sum() / nray:.2f}, with children "
               f"{hist[0].sum() / nray:.2f}, subtree-box tests {(hist[1] * ar).sum() / nray:.2f}, own-list walks {hist[3].sum() / nray:.2f}, "
               f"inner culling steps {(hist[3] * ar).sum() / nray:.2f}, exact-test steps {(hist[4] * ar).sum() / nray:.2f}")
+        if hist[7].sum():
+            f = hist[7].astype(float) / nray
+            print(f"  shadow filter per primary ray: node visits {f[0]:.2f}, list boxes {f[1]:.2f}, inner culling steps {f[5]:.2f}, "
+                  f"subtree-box tests {f[6]:.2f}, exact tests {f[2]:.2f}; queries answered (clear) {f[3]:.3f}, handed to the exact walk {f[4]:.3f}")
         for k, label in enumerate(KINDS):
             row = hist[k].astype(float)
             tot = row.sum()
