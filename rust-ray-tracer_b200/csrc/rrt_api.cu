@@ -136,6 +136,9 @@ int make_params(const rrt_render_params* p, const rrt_shard* sh, DevParams* out)
     d.n_shards = sh->n_shards;
     d.shard_index = sh->shard_index;
     d.n_rows_local = rrt_shard_rows(p->height, sh);
+    // experiment builds (-DRRT_SHADOW_FILTER=1) only: RRT_SHADOW_FILTER_RT=0 renders without the filter, same library
+    const char* sf = std::getenv("RRT_SHADOW_FILTER_RT");
+    d.shadow_filter = (sf && std::atoi(sf) == 0) ? 0 : 1;
     *out = d;
     return RRT_OK;
 }

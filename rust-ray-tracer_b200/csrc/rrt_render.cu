@@ -114,7 +114,11 @@ render_kernel(const DevScene sc, const __grid_constant__ DevParams P, uint32_t* 
         // ---- one traversal for every lane that carries a ray, whatever its kind
         if (active) {
             Hit h;
+#if RRT_SHADOW_FILTER
+            traverse<COUNT>(sc, st.so, st.sd, st.smax, st.shadow, h, tc_total, P.shadow_filter != 0);
+#else
             traverse<COUNT>(sc, st.so, st.sd, st.smax, st.shadow, h, tc_total);
+#endif
             if (st.advance<COUNT>(sc, P, h, park)) {
                 active = false;
                 if (hit_ids) hit_ids[pix * 4 + k] = st.hit0;

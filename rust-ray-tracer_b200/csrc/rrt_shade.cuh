@@ -16,7 +16,8 @@ struct DevParams {
     int32_t use_rot, _pad;
     double rot[9];
     int32_t tile_rows, n_shards, shard_index, n_rows_local;  // row sharding (rrt_shard)
-    int32_t full_frame, _pad2;  // 1: fb is a FULL frame (possibly peer memory), owned row k goes to its buffer row
+    int32_t full_frame;     // 1: fb is a FULL frame (possibly peer memory), owned row k goes to its buffer row
+    int32_t shadow_filter;  // read by -DRRT_SHADOW_FILTER=1 builds only (rrt_trace.cuh): 0 switches the filter off for this launch
 };
 
 struct RayCount {

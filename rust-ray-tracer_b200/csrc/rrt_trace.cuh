@@ -375,7 +375,7 @@ __device__ __forceinline__ bool shadow_clear(const DevScene& sc, const V3& o, co
 // (shadow rays, raytracer.rs:181-187) — `best` only ever improves, so the first update decides.
 template <bool COUNT>
 __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const V3& d, const double max_t,
-                                         const bool any_hit, Hit& best, TraceCount& tc) {
+                                         const bool any_hit, Hit& best, TraceCount& tc, const bool use_filter = true) {
     best.id = kNone;
     best.rec = 0;
     best.t = max_t;
@@ -396,7 +396,7 @@ __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const 
 #if RRT_CULL_F32
     const CullRay cr = make_cull_ray(sc, o, d, ax, ay, az);
 #if RRT_SHADOW_FILTER
-    if (any_hit && shadow_clear<COUNT>(sc, o, d, max_t, cr, stk, cstk, tc)) return;   // best.id == kNone: None
+    if (any_hit && use_filter && shadow_clear<COUNT>(sc, o, d, max_t, cr, stk, cstk, tc)) return;   // best.id == kNone: None
 #endif
 #else
     // reciprocal direction for the CONSERVATIVE culling boxes only (never for a reference decision)

@@ -9,5 +9,7 @@ o=gpurun_out
 python -m pytest tests -m gpu -x -q > $o/r02_pytest.log 2>&1; echo "pytest rc $? : $(tail -1 $o/r02_pytest.log)"
 python __graft_entry__.py smoke > $o/r02_smoke.log 2>&1; echo "smoke rc $? : $(tail -1 $o/r02_smoke.log)"
 python tools/variant_sweep.py variants/*.so -- c2 c3a c4 c5 > $o/r02_variants.txt 2>&1; echo "variants rc $?"
+# the filter builds once more with the filter switched off at run time (same library): what the second loop costs by being there
+RRT_SHADOW_FILTER_RT=0 python tools/variant_sweep.py variants/m_filter.so variants/o_filter_all.so -- c2 c4 c5 > $o/r02_variants_filter_off.txt 2>&1; echo "filter-off rc $?"
 grep -E "^==|ms" $o/r02_variants.txt | tail -80
 python bench.py > $o/r02_bench_c4_default.json 2> $o/r02_bench_c4_default.err; echo "bench rc $?"
