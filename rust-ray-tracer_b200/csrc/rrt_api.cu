@@ -136,9 +136,11 @@ int make_params(const rrt_render_params* p, const rrt_shard* sh, DevParams* out)
     d.n_shards = sh->n_shards;
     d.shard_index = sh->shard_index;
     d.n_rows_local = rrt_shard_rows(p->height, sh);
-    // experiment builds (-DRRT_SHADOW_FILTER=1) only: RRT_SHADOW_FILTER_RT=0 renders without the filter, same library
+    // experiment builds (-DRRT_SHADOW_FILTER=1) only: RRT_SHADOW_FILTER_RT = 0 no filter, 1 (default) switched from one
+    // launch to the next by what the filtered queries returned (rrt_render.cu), 2 always on — same library, same frames
     const char* sf = std::getenv("RRT_SHADOW_FILTER_RT");
-    d.shadow_filter = (sf && std::atoi(sf) == 0) ? 0 : 1;
+    const int sfm = sf ? std::atoi(sf) : 1;
+    d.shadow_filter = sfm < 0 || sfm > 2 ? 1 : sfm;
     *out = d;
     return RRT_OK;
 }

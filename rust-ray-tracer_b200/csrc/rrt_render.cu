@@ -28,6 +28,22 @@ __device__ unsigned long long g_tl[4 + 256];   // [0] min start, [1] min queue-d
 __device__ __forceinline__ unsigned long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
 #endif
 
+#if RRT_SHADOW_FILTER
+// Experiment builds only (rrt_trace.cuh, RRT_SHADOW_FILTER): frame-to-frame switch of the shadow filter.  The filter pays
+// where shadow queries mostly come back None (c4: 99 %) and costs where they are mostly occluded (c5: none come back
+// None), so every launch counts what the queries that went through the filter returned, a one-thread kernel behind it
+// sets the switch for the next launch, and 1/16 of the pixel groups keep probing while it is off.  Results do not
+// depend on the switch (both paths are exact).  DevParams::shadow_filter: 0 off, 1 this switch, 2 always on.
+__device__ unsigned int g_fstat[4] = {0u, 0u, 1u, 0u};   // None, Some, filter on for the next launch, launches
+__global__ void filter_update_kernel() {
+    const unsigned int none = g_fstat[0], some = g_fstat[1];
+    if (none + some >= 64u) g_fstat[2] = (2u * none >= none + some) ? 1u : 0u;
+    g_fstat[0] = 0u;
+    g_fstat[1] = 0u;
+    g_fstat[3] += 1u;
+}
+#endif
+
 // Persistent render kernel (Scene::draw_scene, engine.rs:186-255).  One lane = one supersample at a time.
 // Whenever lanes of a warp run dry — their ray missed, or finished its shadow / mirror chain early — they
 // fetch the next sample indices from a global queue (one atomicAdd per warp per refill) instead of idling
@@ -57,6 +73,11 @@ render_kernel(const DevScene sc, const __grid_constant__ DevParams P, uint32_t* 
     __shared__ uint2 tile_info_s[HINT ? kBlock / 32 : 1];
     uint2& tile_info = tile_info_s[HINT ? threadIdx.x >> 5 : 0];
     if (HINT && lane == 0) tile_info = make_uint2(0xFFFFFFFFu, 0u);
+#if RRT_SHADOW_FILTER
+    __shared__ unsigned int fstat_s[kBlock / 32][2];   // this warp's filtered shadow queries: came back None / Some
+    unsigned int* const fstat_w = fstat_s[threadIdx.x >> 5];
+    if (lane < 2) fstat_w[lane] = 0u;
+#endif
     __syncwarp();
 #if RRT_TIMELINE
     if (lane == 0) atomicMin(&g_tl[0], gtime());
@@ -115,7 +136,10 @@ render_kernel(const DevScene sc, const __grid_constant__ DevParams P, uint32_t* 
         if (active) {
             Hit h;
 #if RRT_SHADOW_FILTER
-            traverse<COUNT>(sc, st.so, st.sd, st.smax, st.shadow, h, tc_total, P.shadow_filter != 0);
+            const bool use_filter = st.shadow && P.shadow_filter != 0 &&
+                                    (P.shadow_filter == 2 || g_fstat[2] != 0u || ((pix >> 6) & 15u) == 0u);
+            traverse<COUNT>(sc, st.so, st.sd, st.smax, st.shadow, h, tc_total, use_filter);
+            if (use_filter) atomicAdd(fstat_w + (h.id == kNone ? 0 : 1), 1u);
 #else
             traverse<COUNT>(sc, st.so, st.sd, st.smax, st.shadow, h, tc_total);
 #endif
@@ -128,6 +152,10 @@ render_kernel(const DevScene sc, const __grid_constant__ DevParams P, uint32_t* 
             }
         }
     }
+#if RRT_SHADOW_FILTER
+    __syncwarp();
+    if (lane < 2 && fstat_w[lane] != 0u) atomicAdd(&g_fstat[lane], fstat_w[lane]);
+#endif
 #if RRT_TIMELINE
     if (lane == 0) {
         const unsigned long long t = gtime();
@@ -342,6 +370,9 @@ cudaError_t launch_render(const DevScene& sc, const DevParams& P, uint32_t* d_fb
     else
         render_kernel<false, false><<<grid, kBlock, 0, stream>>>(sc, P, d_fb, d_hit, d_scratch, next, nullptr, tiles_x, total, nullptr, nullptr);
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
+#if RRT_SHADOW_FILTER
+    if (!d_counters && P.shadow_filter == 1) filter_update_kernel<<<1, 1, 0, stream>>>();
+#endif
     if (hint) {
         // next frame's order: stable sort of the blocks by this frame's cost class, on the side stream, so that it
         // overlaps whatever the caller does with the frame next (copy to the host, gather, L2 flush of a benchmark)

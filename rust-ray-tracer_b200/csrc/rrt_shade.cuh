@@ -17,7 +17,7 @@ struct DevParams {
     double rot[9];
     int32_t tile_rows, n_shards, shard_index, n_rows_local;  // row sharding (rrt_shard)
     int32_t full_frame;     // 1: fb is a FULL frame (possibly peer memory), owned row k goes to its buffer row
-    int32_t shadow_filter;  // read by -DRRT_SHADOW_FILTER=1 builds only (rrt_trace.cuh): 0 switches the filter off for this launch
+    int32_t shadow_filter;  // read by -DRRT_SHADOW_FILTER=1 builds only: 0 off, 1 switched per launch (rrt_render.cu), 2 always on
 };
 
 struct RayCount {

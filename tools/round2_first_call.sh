@@ -9,7 +9,10 @@ o=gpurun_out
 python -m pytest tests -m gpu -x -q > $o/r02_pytest.log 2>&1; echo "pytest rc $? : $(tail -1 $o/r02_pytest.log)"
 python __graft_entry__.py smoke > $o/r02_smoke.log 2>&1; echo "smoke rc $? : $(tail -1 $o/r02_smoke.log)"
 python tools/variant_sweep.py variants/*.so -- c2 c3a c4 c5 > $o/r02_variants.txt 2>&1; echo "variants rc $?"
-# the filter builds once more with the filter switched off at run time (same library): what the second loop costs by being there
-RRT_SHADOW_FILTER_RT=0 python tools/variant_sweep.py variants/m_filter.so variants/o_filter_all.so -- c2 c4 c5 > $o/r02_variants_filter_off.txt 2>&1; echo "filter-off rc $?"
+# the filter builds twice more (same libraries, same frames): filter always on (RRT_SHADOW_FILTER_RT=2: its pure effect;
+# the sweep above ran the frame-to-frame switch, which turns it off on c5) and never on (=0: what the second loop costs by being there)
+for m in 2 0; do
+  RRT_SHADOW_FILTER_RT=$m python tools/variant_sweep.py variants/m_filter.so variants/o_filter_all.so -- c2 c4 c5 > $o/r02_variants_filter_rt$m.txt 2>&1; echo "filter rt=$m rc $?"
+done
 grep -E "^==|ms" $o/r02_variants.txt | tail -80
 python bench.py > $o/r02_bench_c4_default.json 2> $o/r02_bench_c4_default.err; echo "bench rc $?"
