@@ -76,6 +76,7 @@ render_kernel(const DevScene sc, const __grid_constant__ DevParams P, uint32_t* 
 #if RRT_SHADOW_FILTER
     __shared__ unsigned int fstat_s[kBlock / 32][2];   // this warp's filtered shadow queries: came back None / Some
     unsigned int* const fstat_w = fstat_s[threadIdx.x >> 5];
+    bool prev_miss = false;   // RRT_PRIMARY_FILTER: this lane's previous sample hit nothing
     if (lane < 2) fstat_w[lane] = 0u;
 #endif
     __syncwarp();
@@ -136,15 +137,20 @@ render_kernel(const DevScene sc, const __grid_constant__ DevParams P, uint32_t* 
         if (active) {
             Hit h;
 #if RRT_SHADOW_FILTER
-            const bool use_filter = st.shadow && P.shadow_filter != 0 &&
-                                    (P.shadow_filter == 2 || g_fstat[2] != 0u || ((pix >> 6) & 15u) == 0u);
-            traverse<COUNT>(sc, st.so, st.sd, st.smax, st.shadow, h, tc_total, use_filter);
-            if (use_filter) atomicAdd(fstat_w + (h.id == kNone ? 0 : 1), 1u);
+            const bool was_shadow = st.shadow;
+            bool use_filter = P.shadow_filter != 0;
+            if (was_shadow) use_filter = use_filter && (P.shadow_filter == 2 || g_fstat[2] != 0u || ((pix >> 6) & 15u) == 0u);
+            else use_filter = use_filter && RRT_PRIMARY_FILTER && prev_miss && st.depth == 0;
+            traverse<COUNT>(sc, st.so, st.sd, st.smax, was_shadow, h, tc_total, use_filter);
+            if (use_filter && was_shadow) atomicAdd(fstat_w + (h.id == kNone ? 0 : 1), 1u);
 #else
             traverse<COUNT>(sc, st.so, st.sd, st.smax, st.shadow, h, tc_total);
 #endif
             if (st.advance<COUNT>(sc, P, h, park)) {
                 active = false;
+#if RRT_SHADOW_FILTER
+                prev_miss = st.hit0 < 0;
+#endif
                 if (hit_ids) hit_ids[pix * 4 + k] = st.hit0;
                 const uint32_t add = sample_add(st.res);
                 const uint32_t old = atomicAdd(acc + pix, add);

@@ -290,6 +290,10 @@ __device__ __forceinline__ uint32_t children_hit_pred(const double (&mnx)[2], co
                               // any order.  None => the reference returns None (it can only return an accepted triangle
                               // with t < max_t, ray.rs:163 at the root); otherwise the exact walk decides as before.
 #endif
+#ifndef RRT_PRIMARY_FILTER
+#define RRT_PRIMARY_FILTER 0  // with RRT_SHADOW_FILTER: camera rays whose lane just finished a sample that MISSED everything
+                              // (the next sample of a lane is the same position of the neighbouring tile) try the filter first
+#endif
 #if RRT_SHADOW_FILTER && RRT_CULL_F32
 // true: provably no triangle of the scene is accepted by the exact test with t < max_t.  Visits a SUPERSET of the nodes
 // the reference can reach (subtree boxes instead of exact child slabs), so a `true` is exact; `false` decides nothing.
@@ -396,7 +400,9 @@ __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const 
 #if RRT_CULL_F32
     const CullRay cr = make_cull_ray(sc, o, d, ax, ay, az);
 #if RRT_SHADOW_FILTER
-    if (any_hit && use_filter && shadow_clear<COUNT>(sc, o, d, max_t, cr, stk, cstk, tc)) return;   // best.id == kNone: None
+    // closest-hit rays too when the caller expects a miss (RRT_PRIMARY_FILTER): no accepted triangle below max_t anywhere
+    // is None for them just the same
+    if ((any_hit || RRT_PRIMARY_FILTER) && use_filter && shadow_clear<COUNT>(sc, o, d, max_t, cr, stk, cstk, tc)) return;
 #endif
 #else
     // reciprocal direction for the CONSERVATIVE culling boxes only (never for a reference decision)

@@ -28,3 +28,5 @@ build l_all_mb6     -DRRT_SLAB_PRED=1 -DRRT_LATE_PRUNE=1 -DRRT_CULL_LOOP=3 -DRRT
 build m_filter      -DRRT_SHADOW_FILTER=1
 build n_filter_pred -DRRT_SHADOW_FILTER=1 -DRRT_SLAB_PRED=1
 build o_filter_all  -DRRT_SHADOW_FILTER=1 -DRRT_SLAB_PRED=1 -DRRT_LATE_PRUNE=1 -DRRT_CULL_LOOP=3 -DRRT_PEND=2
+build p_filter_prim -DRRT_SHADOW_FILTER=1 -DRRT_PRIMARY_FILTER=1
+build q_filter_prim_all -DRRT_SHADOW_FILTER=1 -DRRT_PRIMARY_FILTER=1 -DRRT_SLAB_PRED=1 -DRRT_LATE_PRUNE=1 -DRRT_CULL_LOOP=3 -DRRT_PEND=2
