@@ -25,25 +25,31 @@ EMU_LIB = os.path.join(EMU_DIR, "libemu_trace" + "".join(c if c.isalnum() else "
 CSRC = os.path.join(ROOT, "rust-ray-tracer_b200", "csrc")
 
 
-def _build_emu():
+def _lib_name(extra):
+    return os.path.join(EMU_DIR, "libemu_trace" + "".join(c if c.isalnum() else "_" for c in "".join(extra)) + ".so")
+
+
+def _build_emu(extra=None):
+    """-> path of the emulation library built with the extra -D flags (default: RRT_EMU_FLAGS)."""
+    extra = EMU_FLAGS if extra is None else list(extra)
+    lib = _lib_name(extra)
     deps = [EMU_SRC, os.path.join(ROOT, "include", "rrt.h")] + [
         os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h", ".cpp"))]
-    if os.path.exists(EMU_LIB) and all(os.path.getmtime(EMU_LIB) >= os.path.getmtime(d) for d in deps):
-        return
-    flags = ["-O2", "-std=c++17", "-ffp-contract=off", "-fno-fast-math", "-fopenmp", "-fPIC", "-shared", "-w"] + EMU_FLAGS
+    if os.path.exists(lib) and all(os.path.getmtime(lib) >= os.path.getmtime(d) for d in deps):
+        return lib
+    flags = ["-O2", "-std=c++17", "-ffp-contract=off", "-fno-fast-math", "-fopenmp", "-fPIC", "-shared", "-w"] + extra
     try:
         if " fma " in open("/proc/cpuinfo").read():
             flags.append("-mfma")          # hardware single-rounding fma(); without it glibc's exact software fma is used
     except OSError:
         pass
     cuda_inc = os.path.join(os.environ.get("CUDA_HOME", "/usr/local/cuda"), "include")
-    subprocess.run(["g++", *flags, "-I" + cuda_inc, "-o", EMU_LIB, EMU_SRC, os.path.join(CSRC, "rrt_octree.cpp")], check=True)
+    subprocess.run(["g++", *flags, "-I" + cuda_inc, "-o", lib, EMU_SRC, os.path.join(CSRC, "rrt_octree.cpp")], check=True)
+    return lib
 
 
-@pytest.fixture(scope="module")
-def emu():
-    _build_emu()
-    L = C.CDLL(EMU_LIB)
+def _load_emu(lib):
+    L = C.CDLL(lib)
     vp, dp = C.c_void_p, C.POINTER(C.c_double)
     L.emu_scene_create.argtypes = [vp, C.c_uint64, vp, vp, C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.POINTER(vp)]
     L.emu_scene_destroy.argtypes = [vp]
@@ -56,6 +62,16 @@ def emu():
     L.emu_ray_colours.argtypes = [vp, vp, C.c_uint64, vp, vp, vp]
     L.emu_render_shard.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp]
     return L
+
+
+@pytest.fixture(scope="module")
+def emu():
+    return _load_emu(_build_emu())
+
+
+# the compile-time experiments of rrt_trace.cuh prepared for round 2, all switched on together (profiles/r01_experiments.md)
+PREPARED_VARIANTS = ["-DRRT_SLAB_PRED=1", "-DRRT_LATE_PRUNE=1", "-DRRT_CULL_LOOP=3", "-DRRT_PEND=2", "-DRRT_SHADOW_FILTER=1",
+                     "-DRRT_PRIMARY_FILTER=1"]
 
 
 class EmuScene:
@@ -367,5 +383,26 @@ def test_shards_through_the_kernel_helpers(emu, rrt, scenes, W, H, T, G):
         assert np.array_equal(fb, ofb[rows]) and np.array_equal(hit, ohit[rows])
         es.render_shard(p, T, G, r, full_frame=frame, want_hit_ids=False)
     assert np.array_equal(frame, ofb)
+    es.close()
+    osc.close()
+
+
+def test_prepared_variants_stay_exact(rrt, scenes):
+    # The experiment switches of the traversal (children hit mask from pairwise quotient comparisons, queued leaves, late
+    # pruning, the any-accepted-hit filter on every ray) must keep returning the oracle's answers: a smaller fuzz run and
+    # one whole frame over a library built with all of them on, so that they cannot rot unnoticed between GPU sessions.
+    from oracle.oracle import OracleScene
+    L = _load_emu(_build_emu(PREPARED_VARIANTS))
+    sd = scenes("model2")
+    rng = np.random.default_rng(77)
+    o, d, mt = fuzz_rays(rng, 120_000, np.array([0.0, 3.0, 0.0]), 9.0)
+    o[1::29] = np.array([0.0, 2.0, -10.0])
+    osc = OracleScene(sd)
+    es = EmuScene(L, sd)
+    check(es, osc, o, d, mt, min_hits=9_000)
+    p = rrt.make_params(96, 54)
+    fb, hit = es.render_shard(p)
+    ofb, ohit, _, _ = osc.render(p)
+    assert np.array_equal(hit, ohit) and np.array_equal(fb, ofb)
     es.close()
     osc.close()
