@@ -336,6 +336,9 @@ struct CullBuilder {
     uint32_t leaf_max;                // records per leaf (<= 8: 3-bit count field)
 
     double scale;                     // FlatScene::scale
+    bool indirect = false;            // ids[] are RECORD indices and every leaf is one record (the scene-wide hierarchy)
+    uint32_t* next = nullptr;         // indirect: `out` is pre-sized and inner nodes are handed out from this counter
+                                      // (atomically: large subtrees are built as OpenMP tasks on disjoint ranges)
 
 #if RRT_CULL_F32
     void pad_box(double* b) const {
@@ -464,6 +467,7 @@ struct CullBuilder {
     // Builds the subtree over [lo,hi) (hi-lo > leaf_max) and returns its DevCull index. SAH splits can be
     // arbitrarily unbalanced, so below depth 30 the split is by count: total depth <= 30 + 28 < kMaxCullDepth.
     uint32_t build(uint32_t lo, uint32_t hi, int depth = 0) {
+        if (next) return build_tasks(lo, hi, depth);
         const uint32_t me = (uint32_t)out.size();
         out.emplace_back();
         const uint32_t mid = (tight && depth < 30) ? split(lo, hi) : lo + (hi - lo) / 2;
@@ -473,11 +477,43 @@ struct CullBuilder {
             bounds(r[s], r[s + 1], b);
             pad_box(b);
             const uint32_t n = r[s + 1] - r[s];
-            const uint32_t child = (n <= leaf_max) ? leaf_word(rec_base + r[s], n) : build(r[s], r[s + 1], depth + 1);
+            const uint32_t child = (n <= leaf_max) ? (indirect ? leaf_word(ids[r[s]], 1u) : leaf_word(rec_base + r[s], n))
+                                                   : build(r[s], r[s + 1], depth + 1);
             DevCull& c = out[me];  // re-fetch: vector may have grown
             store_box(c, s, b);
             c.child[s] = child;
         }
+        return me;
+    }
+    // Same tree, `out` pre-sized (a binary tree with one record per leaf has n - 1 inner nodes): the two halves of a
+    // large range are independent (split() permutes [lo,hi) only) and are built as tasks.
+    uint32_t build_tasks(uint32_t lo, uint32_t hi, int depth) {
+        uint32_t me;
+#pragma omp atomic capture
+        me = (*next)++;
+        const uint32_t mid = (tight && depth < 30) ? split(lo, hi) : lo + (hi - lo) / 2;
+        const uint32_t r[3] = {lo, mid, hi};
+        uint32_t child[2];
+        for (int s = 0; s < 2; ++s) {
+            double b[6];
+            bounds(r[s], r[s + 1], b);
+            pad_box(b);
+            store_box(out[me], s, b);
+            const uint32_t n = r[s + 1] - r[s];
+            if (n <= leaf_max) {
+                child[s] = leaf_word(ids[r[s]], 1u);
+            } else if (n > 50000u) {
+                uint32_t* dst = &child[s];
+                const uint32_t a = r[s], e = r[s + 1];
+#pragma omp task firstprivate(dst, a, e, depth)
+                *dst = build_tasks(a, e, depth + 1);
+            } else {
+                child[s] = build_tasks(r[s], r[s + 1], depth + 1);
+            }
+        }
+#pragma omp taskwait
+        out[me].child[0] = child[0];
+        out[me].child[1] = child[1];
         return me;
     }
 };
@@ -655,6 +691,34 @@ void flatten(const HostOctree& t, const double* v, uint32_t cull_threshold, uint
             out->cull.push_back(c);
         }
         std::vector<DevCull>().swap(pc);
+    }
+    // EXPERIMENT (RRT_GLOBAL_CULL=1 at scene creation; read by -DRRT_SHADOW_FILTER=2 builds only): one culling hierarchy
+    // over ALL records of the scene, every leaf a single record, for the any-accepted-hit filter of rrt_trace.cuh — which
+    // record belongs to which octree node does not matter to that question.  Its root + 1 is parked in the padding of
+    // node 0 (0 = none); the default flatten is unchanged byte for byte.
+    const char* gc = std::getenv("RRT_GLOBAL_CULL");
+    if (gc && std::atoi(gc) != 0 && tight && out->scale < INFINITY && out->tris.size() > 1 && out->tris.size() < (1u << 28)) {
+        const size_t nr = out->tris.size();
+        std::vector<uint32_t> recs(nr);
+        std::vector<double> boxes(6 * nr);
+        for (size_t r = 0; r < nr; ++r) {
+            recs[r] = (uint32_t)r;
+            tri_box(v + 9 * (size_t)out->tris[r].id, &boxes[6 * r]);
+        }
+        std::vector<DevCull> piece(nr - 1);
+        uint32_t next = 0;
+        CullBuilder cb{v, recs, std::move(boxes), piece, 0u, true, 1u, out->scale, true, &next};
+        uint32_t root = 0;
+#pragma omp parallel
+#pragma omp single
+        root = cb.build(0, (uint32_t)nr);
+        const uint32_t base = (uint32_t)out->cull.size();
+        for (DevCull& c : piece) {
+            for (int k = 0; k < 2; ++k)
+                if (!(c.child[k] & 0x80000000u)) c.child[k] += base;
+            out->cull.push_back(c);
+        }
+        out->nodes[0]._pad2[0] = root + base + 1u;
     }
 }
 

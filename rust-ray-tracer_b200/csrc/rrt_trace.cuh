@@ -295,6 +295,42 @@ __device__ __forceinline__ uint32_t children_hit_pred(const double (&mnx)[2], co
                               // (the next sample of a lane is the same position of the neighbouring tile) try the filter first
 #endif
 #if RRT_SHADOW_FILTER && RRT_CULL_F32
+// One culling hierarchy (or leaf word) walked in any order: false as soon as a record is accepted with t < max_t.
+template <bool COUNT>
+__device__ __forceinline__ bool list_clear(const DevScene& sc, const V3& o, const V3& d, const double max_t, const CullRay& cr,
+                                           const float limit, uint32_t cur, uint32_t* __restrict__ cstk, TraceCount& tc) {
+    int csp = 0;
+    for (;;) {
+        if (cur & kLeafBit) {
+            const uint32_t first = cur & 0x0FFFFFFFu, cnt = ((cur >> 28) & 7u) + 1u;
+#pragma unroll 1
+            for (uint32_t i = 0; i < cnt; ++i) {
+                double t, u, v;
+                uint32_t id;
+                if (COUNT) tc.mt++;
+                RRT_STAT(7, 2);
+                if (moller_trumbore(o, d, sc.tris + first + i, t, u, v, id) && t < max_t) { RRT_STAT(7, 4); return false; }
+            }
+            if (csp == 0) return true;
+            cur = cstk[--csp];
+        } else {
+            const DevCull* __restrict__ c = sc.cull + cur;
+            const float4* bp = reinterpret_cast<const float4*>(c);
+            const float4 f0 = __ldg(bp), f1 = __ldg(bp + 1), f2 = __ldg(bp + 2);
+            const uint2 ch = __ldg(reinterpret_cast<const uint2*>(&c->child[0]));
+            float tn0, tn1;
+            if (COUNT) tc.cull += 2;
+            RRT_STAT(7, 5);
+            const bool go0 = cull_box(cr, f0.x, f0.y, f0.z, f0.w, f1.x, f1.y, limit, tn0);
+            const bool go1 = cull_box(cr, f1.z, f1.w, f2.x, f2.y, f2.z, f2.w, limit, tn1);
+            if (go0 && go1) { cstk[csp++] = ch.y; cur = ch.x; }
+            else if (go0 || go1) cur = go0 ? ch.x : ch.y;
+            else if (csp != 0) cur = cstk[--csp];
+            else return true;
+        }
+    }
+}
+
 // true: provably no triangle of the scene is accepted by the exact test with t < max_t.  Visits a SUPERSET of the nodes
 // the reference can reach (subtree boxes instead of exact child slabs), so a `true` is exact; `false` decides nothing.
 template <bool COUNT>
@@ -304,6 +340,15 @@ __device__ __forceinline__ bool shadow_clear(const DevScene& sc, const V3& o, co
     // and the mask of the kept children still to visit
     if (!cr.ok) return false;
     const float limit = __double2float_ru(max_t);
+#if RRT_SHADOW_FILTER == 2
+    // a scene-wide hierarchy over all records (flatten, RRT_GLOBAL_CULL=1) answers the same question without the octree
+    const uint32_t groot = __ldg(&sc.nodes[0]._pad2[0]);
+    if (groot != 0u) {
+        const bool clear = list_clear<COUNT>(sc, o, d, max_t, cr, limit, groot - 1u, cstk, tc);
+        if (clear) RRT_STAT(7, 3);
+        return clear;
+    }
+#endif
     int sp = 0;
     uint32_t node = 0;
     for (;;) {
@@ -320,39 +365,7 @@ __device__ __forceinline__ bool shadow_clear(const DevScene& sc, const V3& o, co
             RRT_STAT(7, 1);
             scan = cull_box(cr, lb.x, lb.y, lb.z, lb.w, lc.x, lc.y, limit, tn);
         }
-        if (scan) {
-            uint32_t cur = __ldg(&n->cull_root);
-            int csp = 0;
-            for (;;) {
-                if (cur & kLeafBit) {
-                    const uint32_t first = cur & 0x0FFFFFFFu, cnt = ((cur >> 28) & 7u) + 1u;
-#pragma unroll 1
-                    for (uint32_t i = 0; i < cnt; ++i) {
-                        double t, u, v;
-                        uint32_t id;
-                        if (COUNT) tc.mt++;
-                        RRT_STAT(7, 2);
-                        if (moller_trumbore(o, d, sc.tris + first + i, t, u, v, id) && t < max_t) { RRT_STAT(7, 4); return false; }
-                    }
-                    if (csp == 0) break;
-                    cur = cstk[--csp];
-                } else {
-                    const DevCull* __restrict__ c = sc.cull + cur;
-                    const float4* bp = reinterpret_cast<const float4*>(c);
-                    const float4 f0 = __ldg(bp), f1 = __ldg(bp + 1), f2 = __ldg(bp + 2);
-                    const uint2 ch = __ldg(reinterpret_cast<const uint2*>(&c->child[0]));
-                    float tn0, tn1;
-                    if (COUNT) tc.cull += 2;
-                    RRT_STAT(7, 5);
-                    const bool go0 = cull_box(cr, f0.x, f0.y, f0.z, f0.w, f1.x, f1.y, limit, tn0);
-                    const bool go1 = cull_box(cr, f1.z, f1.w, f2.x, f2.y, f2.z, f2.w, limit, tn1);
-                    if (go0 && go1) { cstk[csp++] = ch.y; cur = ch.x; }
-                    else if (go0 || go1) cur = go0 ? ch.x : ch.y;
-                    else if (csp != 0) cur = cstk[--csp];
-                    else break;
-                }
-            }
-        }
+        if (scan && !list_clear<COUNT>(sc, o, d, max_t, cr, limit, __ldg(&n->cull_root), cstk, tc)) return false;
         // children: every kept child whose subtree box the segment [0, max_t] may touch
         uint32_t todo = 0;
         for (uint32_t left = m.y, rank = 0; left; left &= left - 1u, ++rank) {

@@ -30,3 +30,7 @@ build n_filter_pred -DRRT_SHADOW_FILTER=1 -DRRT_SLAB_PRED=1
 build o_filter_all  -DRRT_SHADOW_FILTER=1 -DRRT_SLAB_PRED=1 -DRRT_LATE_PRUNE=1 -DRRT_CULL_LOOP=3 -DRRT_PEND=2
 build p_filter_prim -DRRT_SHADOW_FILTER=1 -DRRT_PRIMARY_FILTER=1
 build q_filter_prim_all -DRRT_SHADOW_FILTER=1 -DRRT_PRIMARY_FILTER=1 -DRRT_SLAB_PRED=1 -DRRT_LATE_PRUNE=1 -DRRT_CULL_LOOP=3 -DRRT_PEND=2
+# scene-wide culling hierarchy for the filter: run these with RRT_GLOBAL_CULL=1 (round2_first_call.sh does)
+build r_gfilter     -DRRT_SHADOW_FILTER=2
+build s_gfilter_prim -DRRT_SHADOW_FILTER=2 -DRRT_PRIMARY_FILTER=1
+build t_gfilter_all -DRRT_SHADOW_FILTER=2 -DRRT_PRIMARY_FILTER=1 -DRRT_SLAB_PRED=1 -DRRT_LATE_PRUNE=1 -DRRT_CULL_LOOP=3 -DRRT_PEND=2
