@@ -387,12 +387,17 @@ def test_shards_through_the_kernel_helpers(emu, rrt, scenes, W, H, T, G):
     osc.close()
 
 
-def test_prepared_variants_stay_exact(rrt, scenes):
+@pytest.mark.parametrize("global_cull", [False, True])
+def test_prepared_variants_stay_exact(rrt, scenes, monkeypatch, global_cull):
     # The experiment switches of the traversal (children hit mask from pairwise quotient comparisons, queued leaves, late
     # pruning, the any-accepted-hit filter on every ray) must keep returning the oracle's answers: a smaller fuzz run and
     # one whole frame over a library built with all of them on, so that they cannot rot unnoticed between GPU sessions.
     from oracle.oracle import OracleScene
-    L = _load_emu(_build_emu(PREPARED_VARIANTS))
+    flags = list(PREPARED_VARIANTS)
+    if global_cull:   # the filter over one scene-wide culling hierarchy, which flatten builds on request
+        flags[flags.index("-DRRT_SHADOW_FILTER=1")] = "-DRRT_SHADOW_FILTER=2"
+        monkeypatch.setenv("RRT_GLOBAL_CULL", "1")
+    L = _load_emu(_build_emu(flags))
     sd = scenes("model2")
     rng = np.random.default_rng(77)
     o, d, mt = fuzz_rays(rng, 120_000, np.array([0.0, 3.0, 0.0]), 9.0)
