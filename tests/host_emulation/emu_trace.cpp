@@ -262,4 +262,46 @@ int emu_trace_rays(void* p, uint64_t n, const double* o, const double* d, const 
     return 0;
 }
 
+// Closest accepted record of the WHOLE scene through the scene-wide culling hierarchy (flatten with RRT_GLOBAL_CULL=1),
+// ordered walk with limit pruning, ties to the smaller triangle id — i.e. a plain closest-hit tracer over the product's
+// records.  Development aid for the round-2 design note (profiles/r01_experiments.md): how often is that NOT what the
+// reference's octree walk returns?  out_tri[i] = id or -1; returns 1 when the scene has no scene-wide hierarchy.
+int emu_closest_global(void* p, uint64_t n, const double* o, const double* d, int32_t* out_tri) {
+    const EmuScene* s = static_cast<EmuScene*>(p);
+    const uint32_t groot = s->dev.nodes[0]._pad2[0];
+    if (groot == 0u) return 1;
+#pragma omp parallel for schedule(dynamic, 256)
+    for (long long i = 0; i < (long long)n; ++i) {
+        const rrt::V3 oo{o[3 * i], o[3 * i + 1], o[3 * i + 2]}, dd{d[3 * i], d[3 * i + 1], d[3 * i + 2]};
+        const rrt::AxisRay ax = rrt::make_axis(oo.x, dd.x, false), ay = rrt::make_axis(oo.y, dd.y, false),
+                           az = rrt::make_axis(oo.z, dd.z, false);
+        const rrt::CullRay cr = rrt::make_cull_ray(s->dev, oo, dd, ax, ay, az);
+        rrt::Hit nb;
+        nb.id = rrt::kNone; nb.rec = 0; nb.t = __longlong_as_double(0x7FF0000000000000ll);
+        float limit = __int_as_float(0x7f800000);
+        uint32_t stk[rrt::kMaxCullDepth + 2];
+        int sp = 0;
+        uint32_t cur = groot - 1u;
+        for (;;) {
+            if (cur & rrt::kLeafBit) {
+                if (rrt::test_record(oo, dd, s->dev.tris, cur & 0x0FFFFFFFu, nb)) limit = __double2float_ru(nb.t);
+                if (sp == 0) break;
+                cur = stk[--sp];
+            } else {
+                const rrt::DevCull& c = s->dev.cull[cur];
+                float tn0, tn1;
+                const bool go0 = rrt::cull_box(cr, c.box[0][0], c.box[0][1], c.box[0][2], c.box[0][3], c.box[0][4], c.box[0][5], limit, tn0);
+                const bool go1 = rrt::cull_box(cr, c.box[1][0], c.box[1][1], c.box[1][2], c.box[1][3], c.box[1][4], c.box[1][5], limit, tn1);
+                const bool swap = tn1 < tn0;
+                if (go0 && go1) { stk[sp++] = swap ? c.child[0] : c.child[1]; cur = swap ? c.child[1] : c.child[0]; }
+                else if (go0 || go1) cur = go0 ? c.child[0] : c.child[1];
+                else if (sp != 0) cur = stk[--sp];
+                else break;
+            }
+        }
+        out_tri[i] = nb.id == rrt::kNone ? -1 : (int32_t)nb.id;
+    }
+    return 0;
+}
+
 }  // extern "C"
