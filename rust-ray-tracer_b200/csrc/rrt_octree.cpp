@@ -719,6 +719,30 @@ void flatten(const HostOctree& t, const double* v, uint32_t cull_threshold, uint
             out->cull.push_back(c);
         }
         out->nodes[0]._pad2[0] = root + base + 1u;
+        // for the sparse closest-hit experiment (RRT_SPARSE_PRIMARY, rrt_trace.cuh): the way UP from a record — its node
+        // in DevTri::_pad, a node's parent in DevNode::_pad and its reference child index in _pad2[1] — and, in node 0's
+        // _pad, whether every stored triangle lies inside the box of the node that stores it (false when a triangle pokes
+        // out of the root box, utils.rs:145 / octree.rs:71-73)
+        uint32_t inside = 1u;
+        for (size_t d = 0; d < out->nodes.size(); ++d) {
+            DevNode& dn = out->nodes[d];
+            uint32_t rank = 0;
+            for (int k = 0; k < 8; ++k)
+                if (dn.child_mask & (1u << k)) {
+                    DevNode& ch = out->nodes[dn.first_child + rank++];
+                    ch._pad = (uint32_t)d;
+                    ch._pad2[1] = (uint32_t)k;
+                }
+            const double* nb = t.nodes[order[d]].box;
+            for (uint32_t r = dn.tri_first; r < dn.tri_first + dn.tri_n; ++r) {
+                out->tris[r]._pad = (uint32_t)d;
+                double tb[6];
+                tri_box(v + 9 * (size_t)out->tris[r].id, tb);
+                for (int k = 0; k < 3; ++k)
+                    if (!(tb[k] >= nb[k] && tb[3 + k] <= nb[3 + k])) inside = 0u;
+            }
+        }
+        out->nodes[0]._pad = inside;
     }
 }
 

@@ -140,7 +140,7 @@ render_kernel(const DevScene sc, const __grid_constant__ DevParams P, uint32_t* 
             const bool was_shadow = st.shadow;
             bool use_filter = P.shadow_filter != 0;
             if (was_shadow) use_filter = use_filter && (P.shadow_filter == 2 || g_fstat[2] != 0u || ((pix >> 6) & 15u) == 0u);
-            else use_filter = use_filter && RRT_PRIMARY_FILTER && prev_miss && st.depth == 0;
+            else use_filter = use_filter && st.depth == 0 && (RRT_SPARSE_PRIMARY || (RRT_PRIMARY_FILTER && prev_miss));
             traverse<COUNT>(sc, st.so, st.sd, st.smax, was_shadow, h, tc_total, use_filter);
             if (use_filter && was_shadow) atomicAdd(fstat_w + (h.id == kNone ? 0 : 1), 1u);
 #else

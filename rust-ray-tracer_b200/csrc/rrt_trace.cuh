@@ -388,6 +388,89 @@ __device__ __forceinline__ bool shadow_clear(const DevScene& sc, const V3& o, co
 }
 #endif
 
+#ifndef RRT_SPARSE_PRIMARY
+#define RRT_SPARSE_PRIMARY 0  // EXPERIMENT (with RRT_SHADOW_FILTER == 2 and a scene built with RRT_GLOBAL_CULL=1): closest-hit
+                              // rays with max_t = +inf first look for the closest accepted record of the whole scene in
+                              // the scene-wide hierarchy and return it when the octree walk provably returns the same:
+                              // see sparse_closest() and the design note in profiles/r01_experiments.md
+#endif
+#if RRT_SPARSE_PRIMARY && RRT_SHADOW_FILTER == 2 && RRT_CULL_F32
+// The walk's result is the minimum-t own hit over the nodes it VISITS.  C = the closest accepted record of the scene is
+// that result when (1) no other accepted record has a t within a margin of C's (ties and octant-boundary cases), (2) every
+// box on the way from the root to C's node is hit by the exact slabs with tmin > 0 and tmin < tmax — so the node is
+// reachable, and no sibling can be sorted before the path through the origin-inside rule (key = tmax) or a point contact —
+// and (3) every stored triangle lies inside its node's box (flatten's flag), which puts the hits of any sibling sorted
+// earlier before C's along the ray.  Anything else: false, and the exact walk runs as if this had not happened.
+template <bool COUNT>
+__device__ __forceinline__ bool sparse_closest(const DevScene& sc, const V3& o, const V3& d, const CullRay& cr, const AxisRay& ax,
+                                               const AxisRay& ay, const AxisRay& az, uint32_t* __restrict__ cstk, Hit& best,
+                                               TraceCount& tc) {
+    const uint32_t groot = __ldg(&sc.nodes[0]._pad2[0]);
+    if (!cr.ok || groot == 0u || __ldg(&sc.nodes[0]._pad) == 0u) return false;
+    const double kInf = __longlong_as_double(0x7FF0000000000000ll);
+    const double kMargin = 1e-6;
+    double t1 = kInf, t2 = kInf;          // smallest and second smallest accepted t (t2: of ANOTHER record)
+    uint32_t id1 = kNone, rec1 = 0;
+    float limit = __int_as_float(0x7f800000);
+    uint32_t cur = groot - 1u;
+    int csp = 0;
+    for (;;) {
+        if (cur & kLeafBit) {
+            const uint32_t r = cur & 0x0FFFFFFFu;
+            double t, u, v;
+            uint32_t id;
+            if (COUNT) tc.mt++;
+            RRT_STAT(7, 8);
+            if (moller_trumbore(o, d, sc.tris + r, t, u, v, id)) {
+                if (t < t1 || (t == t1 && id < id1)) { t2 = t1; t1 = t; id1 = id; rec1 = r; }
+                else if (t < t2) t2 = t;
+                limit = __double2float_ru(t1 + kMargin * t1);     // keep looking a little beyond the best
+            }
+            if (csp == 0) break;
+            cur = cstk[--csp];
+        } else {
+            const DevCull* __restrict__ c = sc.cull + cur;
+            const float4* bp = reinterpret_cast<const float4*>(c);
+            const float4 f0 = __ldg(bp), f1 = __ldg(bp + 1), f2 = __ldg(bp + 2);
+            const uint2 ch = __ldg(reinterpret_cast<const uint2*>(&c->child[0]));
+            float tn0, tn1;
+            if (COUNT) tc.cull += 2;
+            RRT_STAT(7, 9);
+            const bool go0 = cull_box(cr, f0.x, f0.y, f0.z, f0.w, f1.x, f1.y, limit, tn0);
+            const bool go1 = cull_box(cr, f1.z, f1.w, f2.x, f2.y, f2.z, f2.w, limit, tn1);
+            const bool swap = tn1 < tn0;
+            if (go0 && go1) { cstk[csp++] = swap ? ch.x : ch.y; cur = swap ? ch.y : ch.x; }
+            else if (go0 || go1) cur = go0 ? ch.x : ch.y;
+            else if (csp != 0) cur = cstk[--csp];
+            else break;
+        }
+    }
+    if (id1 == kNone) { RRT_STAT(7, 10); return true; }        // no accepted record anywhere: None (best is None already)
+    if (!(t2 > t1 + kMargin * t1)) { RRT_STAT(7, 11); return false; }
+    // up from C's node: every box on the path, with the walk's own slab arithmetic
+    uint32_t node = (uint32_t)(__double_as_longlong(__ldg(&reinterpret_cast<const double*>(sc.tris + rec1)[9])) >> 32);
+    while (node != 0u) {
+        const DevNode* __restrict__ nd = sc.nodes + node;
+        const uint32_t parent = __ldg(&nd->_pad), k = __ldg(&nd->_pad2[1]) & 7u;
+        const DevNode* __restrict__ pn = sc.nodes + parent;
+        double mnx[2], mxx[2], mny[2], mxy[2], mnz[2], mxz[2];
+        slab_axis(ax, __ldg(&pn->px[0]), __ldg(&pn->px[1]), __ldg(&pn->px[2]), mnx[0], mnx[1], mxx[0], mxx[1]);
+        slab_axis(ay, __ldg(&pn->py[0]), __ldg(&pn->py[1]), __ldg(&pn->py[2]), mny[0], mny[1], mxy[0], mxy[1]);
+        slab_axis(az, __ldg(&pn->pz[0]), __ldg(&pn->pz[1]), __ldg(&pn->pz[2]), mnz[0], mnz[1], mxz[0], mxz[1]);
+        const bool xh = (k & 2u) != 0u, yh = k >= 4u, zh = ((k ^ (k >> 1)) & 1u) != 0u;   // as in the child loop below
+        const double tmin = max_nn(max_nn(xh ? mnx[1] : mnx[0], yh ? mny[1] : mny[0]), zh ? mnz[1] : mnz[0]);
+        const double tmax = min_nn(min_nn(xh ? mxx[1] : mxx[0], yh ? mxy[1] : mxy[0]), zh ? mxz[1] : mxz[0]);
+        if (COUNT) tc.box++;
+        RRT_STAT(7, 12);
+        if (!(tmin > 0.0 && tmin < tmax)) { RRT_STAT(7, 13); return false; }
+        node = parent;
+    }
+    best.t = t1; best.id = id1; best.rec = rec1;
+    RRT_STAT(7, 14);
+    return true;
+}
+#endif
+
 // Ray::intersect_with_octant_with_max_t(octree, 0, max_t).  any_hit: the caller only needs Some/None
 // (shadow rays, raytracer.rs:181-187) — `best` only ever improves, so the first update decides.
 template <bool COUNT>
@@ -413,9 +496,16 @@ __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const 
 #if RRT_CULL_F32
     const CullRay cr = make_cull_ray(sc, o, d, ax, ay, az);
 #if RRT_SHADOW_FILTER
+    bool try_filter = (any_hit || RRT_PRIMARY_FILTER) && use_filter;
+#if RRT_SPARSE_PRIMARY && RRT_SHADOW_FILTER == 2
+    if (!any_hit && use_filter && max_t == kInf) {
+        if (sparse_closest<COUNT>(sc, o, d, cr, ax, ay, az, cstk, best, tc)) return;
+        try_filter = false;   // handed over: an accepted record exists (or the ray cannot be culled), the filter would say so too
+    }
+#endif
     // closest-hit rays too when the caller expects a miss (RRT_PRIMARY_FILTER): no accepted triangle below max_t anywhere
     // is None for them just the same
-    if ((any_hit || RRT_PRIMARY_FILTER) && use_filter && shadow_clear<COUNT>(sc, o, d, max_t, cr, stk, cstk, tc)) return;
+    if (try_filter && shadow_clear<COUNT>(sc, o, d, max_t, cr, stk, cstk, tc)) return;
 #endif
 #else
     // reciprocal direction for the CONSERVATIVE culling boxes only (never for a reference decision)

@@ -15,6 +15,6 @@ for m in 2 0; do
   RRT_SHADOW_FILTER_RT=$m python tools/variant_sweep.py variants/m_filter.so variants/o_filter_all.so -- c2 c4 c5 > $o/r02_variants_filter_rt$m.txt 2>&1; echo "filter rt=$m rc $?"
 done
 # the filter over ONE scene-wide culling hierarchy (flatten builds it when RRT_GLOBAL_CULL=1): expected to be the fastest form
-RRT_GLOBAL_CULL=1 python tools/variant_sweep.py variants/a_default.so variants/r_gfilter.so variants/s_gfilter_prim.so variants/t_gfilter_all.so -- c2 c3a c4 > $o/r02_variants_gfilter.txt 2>&1; echo "gfilter rc $?"
+RRT_GLOBAL_CULL=1 python tools/variant_sweep.py variants/a_default.so variants/r_gfilter.so variants/s_gfilter_prim.so variants/t_gfilter_all.so variants/u_sparse.so variants/v_sparse_all.so -- c2 c3a c4 > $o/r02_variants_gfilter.txt 2>&1; echo "gfilter rc $?"
 grep -E "^==|ms" $o/r02_variants.txt $o/r02_variants_gfilter.txt | tail -120
 python bench.py > $o/r02_bench_c4_default.json 2> $o/r02_bench_c4_default.err; echo "bench rc $?"

@@ -34,3 +34,5 @@ build q_filter_prim_all -DRRT_SHADOW_FILTER=1 -DRRT_PRIMARY_FILTER=1 -DRRT_SLAB_
 build r_gfilter     -DRRT_SHADOW_FILTER=2
 build s_gfilter_prim -DRRT_SHADOW_FILTER=2 -DRRT_PRIMARY_FILTER=1
 build t_gfilter_all -DRRT_SHADOW_FILTER=2 -DRRT_PRIMARY_FILTER=1 -DRRT_SLAB_PRED=1 -DRRT_LATE_PRUNE=1 -DRRT_CULL_LOOP=3 -DRRT_PEND=2
+build u_sparse      -DRRT_SHADOW_FILTER=2 -DRRT_SPARSE_PRIMARY=1
+build v_sparse_all  -DRRT_SHADOW_FILTER=2 -DRRT_SPARSE_PRIMARY=1 -DRRT_SLAB_PRED=1 -DRRT_LATE_PRUNE=1 -DRRT_CULL_LOOP=3 -DRRT_PEND=2

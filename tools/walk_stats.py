@@ -68,6 +68,11 @@ def main():
             f = hist[7].astype(float) / nray
             print(f"  shadow filter per primary ray: node visits {f[0]:.2f}, list boxes {f[1]:.2f}, inner culling steps {f[5]:.2f}, "
                   f"subtree-box tests {f[6]:.2f}, exact tests {f[2]:.2f}; queries answered (clear) {f[3]:.3f}, handed to the exact walk {f[4]:.3f}")
+        if hist[7][8:15].sum():
+            f = hist[7].astype(float) / nray
+            print(f"  sparse closest-hit per primary ray: inner steps {f[9]:.2f}, exact tests {f[8]:.2f}, ancestor boxes {f[12]:.2f}; "
+                  f"answered: none {f[10]:.3f} + hit {f[14]:.3f}; handed over: second record within the margin {f[11]:.4f}, "
+                  f"path box (miss / origin inside / point contact) {f[13]:.4f}")
         for k, label in enumerate(KINDS):
             row = hist[k].astype(float)
             tot = row.sum()
