@@ -396,6 +396,7 @@ def test_prepared_variants_stay_exact(rrt, scenes, monkeypatch, global_cull):
     flags = list(PREPARED_VARIANTS)
     if global_cull:   # the filter over one scene-wide culling hierarchy, which flatten builds on request
         flags[flags.index("-DRRT_SHADOW_FILTER=1")] = "-DRRT_SHADOW_FILTER=2"
+        flags.append("-DRRT_SPARSE_PRIMARY=1")   # closest-hit rays answered from that hierarchy where provably the same
         monkeypatch.setenv("RRT_GLOBAL_CULL", "1")
     L = _load_emu(_build_emu(flags))
     sd = scenes("model2")
