@@ -409,6 +409,13 @@ __device__ __forceinline__ bool sparse_closest(const DevScene& sc, const V3& o, 
     if (!cr.ok || groot == 0u || __ldg(&sc.nodes[0]._pad) == 0u) return false;
     const double kInf = __longlong_as_double(0x7FF0000000000000ll);
     const double kMargin = 1e-6;
+    // An accepted hit lies within 1e-12 S of its triangle (the property the f32 culling budget above already rests on),
+    // and with flatten's "inside" flag within 1e-12 S of its node's box.  A record of an octant sorted BEFORE the path to
+    // C's node (it is left through a plane the path is entered through) can therefore not be accepted at a t more than
+    // 2e-12 S / |d_k| beyond C's, k the axis of that plane: the window below is twice that for the flattest non-zero
+    // direction component, plus a relative part for exact ties and good measure.  A record inside the window hands over.
+    const double ymax = fmax(fmax(d.x != 0.0 ? fabs(ax.y) : 0.0, d.y != 0.0 ? fabs(ay.y) : 0.0), d.z != 0.0 ? fabs(az.y) : 0.0);
+    const double kAbs = 4e-12 * (sc.cull_o_max * (1.0 / kCullOriginRel)) * ymax;
     double t1 = kInf, t2 = kInf;          // smallest and second smallest accepted t (t2: of ANOTHER record)
     uint32_t id1 = kNone, rec1 = 0;
     float limit = __int_as_float(0x7f800000);
@@ -424,7 +431,7 @@ __device__ __forceinline__ bool sparse_closest(const DevScene& sc, const V3& o, 
             if (moller_trumbore(o, d, sc.tris + r, t, u, v, id)) {
                 if (t < t1 || (t == t1 && id < id1)) { t2 = t1; t1 = t; id1 = id; rec1 = r; }
                 else if (t < t2) t2 = t;
-                limit = __double2float_ru(t1 + kMargin * t1);     // keep looking a little beyond the best
+                limit = __double2float_ru(t1 + (kMargin * t1 + kAbs));     // keep looking a little beyond the best
             }
             if (csp == 0) break;
             cur = cstk[--csp];
@@ -446,7 +453,7 @@ __device__ __forceinline__ bool sparse_closest(const DevScene& sc, const V3& o, 
         }
     }
     if (id1 == kNone) { RRT_STAT(7, 10); return true; }        // no accepted record anywhere: None (best is None already)
-    if (!(t2 > t1 + kMargin * t1)) { RRT_STAT(7, 11); return false; }
+    if (!(t2 > t1 + (kMargin * t1 + kAbs))) { RRT_STAT(7, 11); return false; }
     // up from C's node: every box on the path, with the walk's own slab arithmetic
     uint32_t node = (uint32_t)(__double_as_longlong(__ldg(&reinterpret_cast<const double*>(sc.tris + rec1)[9])) >> 32);
     while (node != 0u) {
