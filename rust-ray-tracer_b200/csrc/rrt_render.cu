@@ -34,12 +34,18 @@ __device__ __forceinline__ unsigned long long gtime() { unsigned long long t; as
 // None), so every launch counts what the queries that went through the filter returned, a one-thread kernel behind it
 // sets the switch for the next launch, and 1/16 of the pixel groups keep probing while it is off.  Results do not
 // depend on the switch (both paths are exact).  DevParams::shadow_filter: 0 off, 1 this switch, 2 always on.
-__device__ unsigned int g_fstat[4] = {0u, 0u, 1u, 0u};   // None, Some, filter on for the next launch, launches
+// The sparse closest-hit search of camera rays (RRT_SPARSE_PRIMARY) is switched the same way by how many of them it
+// answered itself: a camera inside the geometry (c5) has every ray handed over by the `tmin > 0` rule.
+__device__ unsigned int g_fstat[8] = {0u, 0u, 1u, 0u, 0u, 0u, 1u, 0u};   // None, Some, filter on, launches | answered, handed over, sparse on
 __global__ void filter_update_kernel() {
     const unsigned int none = g_fstat[0], some = g_fstat[1];
     if (none + some >= 64u) g_fstat[2] = (2u * none >= none + some) ? 1u : 0u;
+    const unsigned int ans = g_fstat[4], handed = g_fstat[5];
+    if (ans + handed >= 64u) g_fstat[6] = (2u * ans >= ans + handed) ? 1u : 0u;
     g_fstat[0] = 0u;
     g_fstat[1] = 0u;
+    g_fstat[4] = 0u;
+    g_fstat[5] = 0u;
     g_fstat[3] += 1u;
 }
 #endif
@@ -74,10 +80,10 @@ render_kernel(const DevScene sc, const __grid_constant__ DevParams P, uint32_t* 
     uint2& tile_info = tile_info_s[HINT ? threadIdx.x >> 5 : 0];
     if (HINT && lane == 0) tile_info = make_uint2(0xFFFFFFFFu, 0u);
 #if RRT_SHADOW_FILTER
-    __shared__ unsigned int fstat_s[kBlock / 32][2];   // this warp's filtered shadow queries: came back None / Some
-    unsigned int* const fstat_w = fstat_s[threadIdx.x >> 5];
+    __shared__ unsigned int fstat_s[kBlock / 32][4];   // this warp's filtered shadow queries: came back None / Some;
+    unsigned int* const fstat_w = fstat_s[threadIdx.x >> 5];   // its sparse camera rays: answered / handed over
     bool prev_miss = false;   // RRT_PRIMARY_FILTER: this lane's previous sample hit nothing
-    if (lane < 2) fstat_w[lane] = 0u;
+    if (lane < 4) fstat_w[lane] = 0u;
 #endif
     __syncwarp();
 #if RRT_TIMELINE
@@ -140,9 +146,13 @@ render_kernel(const DevScene sc, const __grid_constant__ DevParams P, uint32_t* 
             const bool was_shadow = st.shadow;
             bool use_filter = P.shadow_filter != 0;
             if (was_shadow) use_filter = use_filter && (P.shadow_filter == 2 || g_fstat[2] != 0u || ((pix >> 6) & 15u) == 0u);
-            else use_filter = use_filter && st.depth == 0 && (RRT_SPARSE_PRIMARY || (RRT_PRIMARY_FILTER && prev_miss));
-            traverse<COUNT>(sc, st.so, st.sd, st.smax, was_shadow, h, tc_total, use_filter);
+            else if (RRT_SPARSE_PRIMARY) use_filter = use_filter && st.depth == 0 &&
+                                                      (P.shadow_filter == 2 || g_fstat[6] != 0u || ((pix >> 6) & 15u) == 0u);
+            else use_filter = use_filter && st.depth == 0 && RRT_PRIMARY_FILTER && prev_miss;
+            uint32_t sparse_outcome = 0u;
+            traverse<COUNT>(sc, st.so, st.sd, st.smax, was_shadow, h, tc_total, use_filter, &sparse_outcome);
             if (use_filter && was_shadow) atomicAdd(fstat_w + (h.id == kNone ? 0 : 1), 1u);
+            if (sparse_outcome != 0u) atomicAdd(fstat_w + 1 + sparse_outcome, 1u);
 #else
             traverse<COUNT>(sc, st.so, st.sd, st.smax, st.shadow, h, tc_total);
 #endif
@@ -160,7 +170,7 @@ render_kernel(const DevScene sc, const __grid_constant__ DevParams P, uint32_t* 
     }
 #if RRT_SHADOW_FILTER
     __syncwarp();
-    if (lane < 2 && fstat_w[lane] != 0u) atomicAdd(&g_fstat[lane], fstat_w[lane]);
+    if (lane < 4 && fstat_w[lane] != 0u) atomicAdd(&g_fstat[lane < 2 ? lane : lane + 2], fstat_w[lane]);
 #endif
 #if RRT_TIMELINE
     if (lane == 0) {

@@ -482,7 +482,8 @@ __device__ __forceinline__ bool sparse_closest(const DevScene& sc, const V3& o, 
 // (shadow rays, raytracer.rs:181-187) — `best` only ever improves, so the first update decides.
 template <bool COUNT>
 __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const V3& d, const double max_t,
-                                         const bool any_hit, Hit& best, TraceCount& tc, const bool use_filter = true) {
+                                         const bool any_hit, Hit& best, TraceCount& tc, const bool use_filter = true,
+                                         uint32_t* __restrict__ sparse_outcome = nullptr) {
     best.id = kNone;
     best.rec = 0;
     best.t = max_t;
@@ -506,7 +507,9 @@ __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const 
     bool try_filter = (any_hit || RRT_PRIMARY_FILTER) && use_filter;
 #if RRT_SPARSE_PRIMARY && RRT_SHADOW_FILTER == 2
     if (!any_hit && use_filter && max_t == kInf) {
-        if (sparse_closest<COUNT>(sc, o, d, cr, ax, ay, az, cstk, best, tc)) return;
+        const bool answered = sparse_closest<COUNT>(sc, o, d, cr, ax, ay, az, cstk, best, tc);
+        if (sparse_outcome) *sparse_outcome = answered ? 1u : 2u;
+        if (answered) return;
         try_filter = false;   // handed over: an accepted record exists (or the ray cannot be culled), the filter would say so too
     }
 #endif
