@@ -395,6 +395,28 @@ __device__ __forceinline__ bool shadow_clear(const DevScene& sc, const V3& o, co
                               // see sparse_closest() and the design note in profiles/r01_experiments.md
 #endif
 #if RRT_SPARSE_PRIMARY && RRT_SHADOW_FILTER == 2 && RRT_CULL_F32
+// Is the accepted t of a record inside the slab interval of its triangle's bounding box (widened by slack)?  False for
+// the grazing records whose t is rounding noise, and for anything not finite.
+__device__ __forceinline__ bool record_t_plausible(const V3& o, const V3& d, const DevTri* __restrict__ rec, double t, double slack) {
+    const double* p = reinterpret_cast<const double*>(rec);
+    double tn = -1e300, tf = 1e300;
+    bool ok = true;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const double a = __ldg(p + k), b = a + __ldg(p + 3 + k), c = a + __ldg(p + 6 + k);
+        const double lo = fmin(a, fmin(b, c)), hi = fmax(a, fmax(b, c));
+        const double ok_ = k == 0 ? o.x : (k == 1 ? o.y : o.z), dk = k == 0 ? d.x : (k == 1 ? d.y : d.z);
+        if (dk != 0.0) {
+            const double t0 = (lo - ok_) / dk, t1 = (hi - ok_) / dk;
+            tn = fmax(tn, fmin(t0, t1));
+            tf = fmin(tf, fmax(t0, t1));
+        } else {
+            ok = ok && ok_ >= lo - 1e-9 * fabs(lo) && ok_ <= hi + 1e-9 * fabs(hi);
+        }
+    }
+    return ok && t >= tn - slack && t <= tf + slack;
+}
+
 // The walk's result is the minimum-t own hit over the nodes it VISITS.  C = the closest accepted record of the scene is
 // that result when (1) no other accepted record has a t within a margin of C's (ties and octant-boundary cases), (2) every
 // box on the way from the root to C's node is hit by the exact slabs with tmin > 0 and tmin < tmax — so the node is
@@ -409,13 +431,16 @@ __device__ __forceinline__ bool sparse_closest(const DevScene& sc, const V3& o, 
     if (!cr.ok || groot == 0u || __ldg(&sc.nodes[0]._pad) == 0u) return false;
     const double kInf = __longlong_as_double(0x7FF0000000000000ll);
     const double kMargin = 1e-6;
-    // An accepted hit lies within 1e-12 S of its triangle (the property the f32 culling budget above already rests on),
-    // and with flatten's "inside" flag within 1e-12 S of its node's box.  A record of an octant sorted BEFORE the path to
-    // C's node (it is left through a plane the path is entered through) can therefore not be accepted at a t more than
-    // 2e-12 S / |d_k| beyond C's, k the axis of that plane: the window below is twice that for the flattest non-zero
-    // direction component, plus a relative part for exact ties and good measure.  A record inside the window hands over.
+    // Every accepted record the search meets must lie where its triangle is: its t inside the slab interval of the
+    // triangle's own bounding box, give or take kSlack (1e-9 S along the flattest non-zero direction component) — a
+    // grazing record whose computed t is noise hands the ray over.  With that CHECKED (not assumed), and flatten's
+    // "inside" flag, a record of an octant sorted BEFORE the path to C's node (left through a plane the path is entered
+    // through) is met by the search (its box begins before that plane, hence before the limit) and is accepted, if at
+    // all, no later than 2 kSlack after C: inside the window below, which hands over.
     const double ymax = fmax(fmax(d.x != 0.0 ? fabs(ax.y) : 0.0, d.y != 0.0 ? fabs(ay.y) : 0.0), d.z != 0.0 ? fabs(az.y) : 0.0);
-    const double kAbs = 4e-12 * (sc.cull_o_max * (1.0 / kCullOriginRel)) * ymax;
+    const double kSlack = 1e-9 * (sc.cull_o_max * (1.0 / kCullOriginRel)) * ymax;
+    const double kAbs = 4.0 * kSlack;
+    bool noisy = false;
     double t1 = kInf, t2 = kInf;          // smallest and second smallest accepted t (t2: of ANOTHER record)
     uint32_t id1 = kNone, rec1 = 0;
     float limit = __int_as_float(0x7f800000);
@@ -429,6 +454,7 @@ __device__ __forceinline__ bool sparse_closest(const DevScene& sc, const V3& o, 
             if (COUNT) tc.mt++;
             RRT_STAT(7, 8);
             if (moller_trumbore(o, d, sc.tris + r, t, u, v, id)) {
+                noisy = noisy || !record_t_plausible(o, d, sc.tris + r, t, kSlack);
                 if (t < t1 || (t == t1 && id < id1)) { t2 = t1; t1 = t; id1 = id; rec1 = r; }
                 else if (t < t2) t2 = t;
                 limit = __double2float_ru(t1 + (kMargin * t1 + kAbs));     // keep looking a little beyond the best
@@ -453,7 +479,7 @@ __device__ __forceinline__ bool sparse_closest(const DevScene& sc, const V3& o, 
         }
     }
     if (id1 == kNone) { RRT_STAT(7, 10); return true; }        // no accepted record anywhere: None (best is None already)
-    if (!(t2 > t1 + (kMargin * t1 + kAbs))) { RRT_STAT(7, 11); return false; }
+    if (noisy || !(t2 > t1 + (kMargin * t1 + kAbs))) { RRT_STAT(7, 11); return false; }
     // up from C's node: every box on the path, with the walk's own slab arithmetic
     uint32_t node = (uint32_t)(__double_as_longlong(__ldg(&reinterpret_cast<const double*>(sc.tris + rec1)[9])) >> 32);
     while (node != 0u) {
