@@ -407,7 +407,7 @@ __device__ __forceinline__ bool record_t_plausible(const V3& o, const V3& d, con
         const double lo = fmin(a, fmin(b, c)), hi = fmax(a, fmax(b, c));
         const double ok_ = k == 0 ? o.x : (k == 1 ? o.y : o.z), dk = k == 0 ? d.x : (k == 1 ? d.y : d.z);
         if (dk != 0.0) {
-            const double t0 = (lo - ok_) / dk, t1 = (hi - ok_) / dk;
+            const double t0 = div_rn(lo - ok_, dk), t1 = div_rn(hi - ok_, dk);   // as calls: cold code, six divisions
             tn = fmax(tn, fmin(t0, t1));
             tf = fmin(tf, fmax(t0, t1));
         } else {
