@@ -17,4 +17,7 @@ done
 # the filter over ONE scene-wide culling hierarchy (flatten builds it when RRT_GLOBAL_CULL=1): expected to be the fastest form
 RRT_GLOBAL_CULL=1 python tools/variant_sweep.py variants/a_default.so variants/r_gfilter.so variants/s_gfilter_prim.so variants/t_gfilter_all.so variants/u_sparse.so variants/v_sparse_all.so -- c2 c3a c4 > $o/r02_variants_gfilter.txt 2>&1; echo "gfilter rc $?"
 grep -E "^==|ms" $o/r02_variants.txt $o/r02_variants_gfilter.txt | tail -120
+# the whole GPU parity suite once more THROUGH the build with every switch on (rrt_trace_rays / rrt_ray_colours / frames
+# against the oracle: the GPU-side proof of the switches, beyond the sha1 comparison of the sweep)
+RRT_GLOBAL_CULL=1 RRT_LIB_PATH=$PWD/variants/v_sparse_all.so python -m pytest tests -m gpu -x -q > $o/r02_pytest_sparse_all.log 2>&1; echo "pytest (all switches) rc $? : $(tail -1 $o/r02_pytest_sparse_all.log)"
 python bench.py > $o/r02_bench_c4_default.json 2> $o/r02_bench_c4_default.err; echo "bench rc $?"
