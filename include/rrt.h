@@ -208,6 +208,32 @@ int rrt_ipc_close_handle(int device, void* d_ptr);
 int rrt_copy_frame_to_host(int device, const uint32_t* d_frame, int32_t width, int32_t height,
                            uint32_t* fb_0rgb, void* cuda_stream);   /* async on the stream if fb is pinned */
 
+/* ---- one canvas in HOST memory for the one-process-per-GPU ranks of a node ----
+ * The reference's output is Canvas.buffer: Vec<u32> in host memory (src/scene/engine.rs:123-128,146-158).  With the
+ * frame sharded over N GPUs every rank copies ITS rows device->host over its own PCIe link, in parallel, straight
+ * into one page-locked frame that all ranks map: a POSIX shared-memory segment (name starts with '/').  Its header
+ * page also holds a process-shared barrier and a slot for the CUDA IPC handle of the peer-store mode above, so a
+ * host without torch.distributed (the Rust crate, a C++ driver) can run the ranks: tests/native/multi_rank_driver.cpp.
+ *   rank 0: rrt_host_frame_create(name, W, H, n_ranks)      other ranks: rrt_host_frame_open(name, timeout)
+ *   every rank, per frame:  rrt_render_to_host_frame(...); cudaStreamSynchronize; rrt_host_frame_barrier  -> the
+ *   frame is complete in rrt_host_frame_pixels(); a second barrier before the next frame's render lets rank 0
+ *   read it undisturbed.  Barriers and waits time out (seconds; <= 0: a default) instead of hanging. */
+typedef struct rrt_host_frame rrt_host_frame;
+int rrt_host_frame_create(const char* name, int32_t width, int32_t height, int32_t n_ranks, rrt_host_frame** out);
+int rrt_host_frame_open(const char* name, double timeout_s, rrt_host_frame** out);
+uint32_t* rrt_host_frame_pixels(rrt_host_frame* f);          /* width*height words, reference canvas layout */
+int rrt_host_frame_geometry(const rrt_host_frame* f, int32_t* width, int32_t* height, int32_t* n_ranks);
+int rrt_host_frame_pin(rrt_host_frame* f, int device);       /* cudaHostRegister: makes the rank's copies asynchronous */
+int rrt_host_frame_barrier(rrt_host_frame* f, double timeout_s);
+int rrt_host_frame_publish_handle(rrt_host_frame* f, const unsigned char handle[64]);
+int rrt_host_frame_fetch_handle(rrt_host_frame* f, double timeout_s, unsigned char handle[64]);
+void rrt_host_frame_close(rrt_host_frame* f);                /* the creator also unlinks the segment */
+/* Renders the shard (as rrt_render_device) and enqueues the copy of its rows to their places in the FULL host frame
+ * `host_frame` (width*height words; rrt_host_frame_pixels() or any caller buffer, asynchronous if page-locked) on
+ * `cuda_stream`; does not synchronise.  With n_shards = 1 this is rrt_render without the blocking copy. */
+int rrt_render_to_host_frame(rrt_scene* scene, const rrt_render_params* params, const rrt_shard* shard,
+                             uint32_t* host_frame, void* cuda_stream);
+
 /* Number of buffer rows shard `shard_index` owns for a frame of `height` rows (row 0 included). */
 int rrt_shard_rows(int32_t height, const rrt_shard* shard);
 

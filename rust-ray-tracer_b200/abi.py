@@ -79,6 +79,9 @@ SYMBOLS = [
     "rrt_render", "rrt_render_frames", "rrt_render_device", "rrt_shard_rows", "rrt_deinterleave_device",
     "rrt_render_device_into_frame", "rrt_frame_alloc", "rrt_frame_free", "rrt_ipc_get_handle", "rrt_ipc_open_handle",
     "rrt_ipc_close_handle", "rrt_copy_frame_to_host",
+    "rrt_host_frame_create", "rrt_host_frame_open", "rrt_host_frame_pixels", "rrt_host_frame_geometry",
+    "rrt_host_frame_pin", "rrt_host_frame_barrier", "rrt_host_frame_publish_handle", "rrt_host_frame_fetch_handle",
+    "rrt_host_frame_close", "rrt_render_to_host_frame",
     "rrt_trace_rays", "rrt_ray_colours", "rrt_render_counters",
     "rrt_octree_build", "rrt_octree_destroy", "rrt_octree_node_count", "rrt_octree_node", "rrt_octree_node_list",
     "rrt_octree_flatten_stats", "rrt_octree_digest",
@@ -120,6 +123,18 @@ def lib():
     L.rrt_ipc_open_handle.argtypes = [C.c_int, vp, C.POINTER(vp)]
     L.rrt_ipc_close_handle.argtypes = [C.c_int, vp]
     L.rrt_copy_frame_to_host.argtypes = [C.c_int, vp, i32, i32, vp, vp]
+    L.rrt_host_frame_create.argtypes = [C.c_char_p, i32, i32, i32, C.POINTER(vp)]
+    L.rrt_host_frame_open.argtypes = [C.c_char_p, C.c_double, C.POINTER(vp)]
+    L.rrt_host_frame_pixels.argtypes = [vp]
+    L.rrt_host_frame_pixels.restype = vp
+    L.rrt_host_frame_geometry.argtypes = [vp, C.POINTER(i32), C.POINTER(i32), C.POINTER(i32)]
+    L.rrt_host_frame_pin.argtypes = [vp, C.c_int]
+    L.rrt_host_frame_barrier.argtypes = [vp, C.c_double]
+    L.rrt_host_frame_publish_handle.argtypes = [vp, vp]
+    L.rrt_host_frame_fetch_handle.argtypes = [vp, C.c_double, vp]
+    L.rrt_host_frame_close.argtypes = [vp]
+    L.rrt_host_frame_close.restype = None
+    L.rrt_render_to_host_frame.argtypes = [vp, C.POINTER(RenderParams), C.POINTER(Shard), vp, vp]
     L.rrt_shard_rows.argtypes = [i32, C.POINTER(Shard)]
     L.rrt_deinterleave_device.argtypes = [C.c_int, vp, i32, i32, i32, i32, i32, vp, vp]
     L.rrt_trace_rays.argtypes = [vp, u64, vp, vp, vp, vp, vp]

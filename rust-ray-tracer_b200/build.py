@@ -11,7 +11,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.environ.get("RRT_OUT") or os.path.join(CSRC, "librrt_b200.so")   # RRT_OUT: variant builds (tools/)
-SOURCES = ["rrt_api.cu", "rrt_render.cu", "rrt_microbench.cu", "rrt_octree.cpp", "rrt_loader.cpp"]
+SOURCES = ["rrt_api.cu", "rrt_render.cu", "rrt_microbench.cu", "rrt_hostframe.cu", "rrt_octree.cpp", "rrt_loader.cpp"]
 HEADERS = ["rrt_device.cuh", "rrt_trace.cuh", "rrt_shade.cuh", "rrt_raygen.cuh", "rrt_render.h", "rrt_octree.h",
            os.path.join("..", "..", "include", "rrt.h")]
 

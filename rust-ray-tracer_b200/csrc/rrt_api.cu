@@ -1,5 +1,6 @@
 // rrt_api.cu — the C ABI of include/rrt.h: scene upload, render calls, per-ray seams.
 // No CPU rendering path exists in this library: every render entry point needs a CUDA device.
+#include <algorithm>
 #include <chrono>
 #include <cmath>
 #include <cstdio>
@@ -112,6 +113,10 @@ int make_params(const rrt_render_params* p, const rrt_shard* sh, DevParams* out)
     if ((int64_t)p->width * p->height > (int64_t)1 << 30) return fail(RRT_ERR_INVALID, "frame too large");
     if (p->n_lights < 0 || p->n_lights > RRT_MAX_LIGHTS) return fail(RRT_ERR_INVALID, "n_lights out of range");
     if (p->max_depth < 0) return fail(RRT_ERR_INVALID, "max_depth < 0");
+    // the reference recurses to whatever depth it is given (raytracer.rs:76); the kernel keeps one mirror level per
+    // slot of a fixed per-lane array, so a deeper request is refused rather than rendered differently
+    if (p->max_depth > kMaxReflectDepth)
+        return fail(RRT_ERR_INVALID, "max_depth > " + std::to_string(kMaxReflectDepth) + " (mirror levels kept per lane)");
     DevParams d{};
     d.W = p->width;
     d.H = p->height;
@@ -120,7 +125,7 @@ int make_params(const rrt_render_params* p, const rrt_shard* sh, DevParams* out)
     d.ys = p->viewport[1] / (double)p->height;   // engine.rs:190
     d.zv = p->viewport[2];                       // engine.rs:191
     d.n_lights = p->n_lights;
-    d.max_depth = p->max_depth > kMaxReflectDepth ? kMaxReflectDepth : p->max_depth;
+    d.max_depth = p->max_depth;
     for (int i = 0; i < p->n_lights; ++i) {
         if (p->lights[i].kind < 0 || p->lights[i].kind > 2) return fail(RRT_ERR_INVALID, "bad light kind");
         d.lights[i] = p->lights[i];
@@ -409,6 +414,32 @@ int rrt_copy_frame_to_host(int device, const uint32_t* d_frame, int32_t width, i
     CU(cudaSetDevice(device));
     CU(cudaMemcpyAsync(fb, d_frame, (size_t)width * height * sizeof(uint32_t), cudaMemcpyDeviceToHost,
                        (cudaStream_t)cuda_stream));
+    return RRT_OK;
+}
+
+// The shard's rows, rendered compactly into the handle's device buffer, leave for their places in a FULL frame in
+// host memory: tile row j of the frame (tile_rows scan-lines) is the shard's j / n_shards-th group, so one pitched
+// copy moves every whole group and a second one the ragged last group (only the frame's last tile row can be short).
+int rrt_render_to_host_frame(rrt_scene* s, const rrt_render_params* p, const rrt_shard* shard, uint32_t* host_frame,
+                             void* cuda_stream) {
+    if (!s || !host_frame) return fail(RRT_ERR_INVALID, "null argument");
+    DevParams P;
+    int rc = make_params(p, shard, &P);
+    if (rc) return rc;
+    CU(cudaSetDevice(s->device));
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    const size_t n = (size_t)P.W * std::max(P.n_rows_local, 1);
+    if ((rc = ensure(&s->d_fb, &s->fb_cap, n))) return rc;
+    if ((rc = ensure(&s->d_scratch, &s->scratch_cap, render_scratch_words(P.n_rows_local, P.W)))) return rc;
+    CU(launch_render(s->dev, P, s->d_fb, nullptr, s->d_scratch, nullptr, st, &s->sched));
+    const size_t row_bytes = (size_t)P.W * sizeof(uint32_t), group = row_bytes * P.tile_rows;
+    const int n_full = P.n_rows_local / P.tile_rows, rest = P.n_rows_local % P.tile_rows;
+    uint32_t* dst0 = host_frame + (size_t)P.shard_index * P.tile_rows * P.W;
+    if (n_full > 0)
+        CU(cudaMemcpy2DAsync(dst0, group * P.n_shards, s->d_fb, group, group, (size_t)n_full, cudaMemcpyDeviceToHost, st));
+    if (rest > 0)
+        CU(cudaMemcpyAsync(dst0 + (size_t)n_full * P.n_shards * P.tile_rows * P.W, s->d_fb + (size_t)n_full * P.tile_rows * P.W,
+                           row_bytes * rest, cudaMemcpyDeviceToHost, st));
     return RRT_OK;
 }
 

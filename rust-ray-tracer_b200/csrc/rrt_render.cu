@@ -5,6 +5,8 @@
 
 #include <cub/device/device_radix_sort.cuh>
 
+#include <mutex>
+
 namespace rrt {
 
 namespace {
@@ -336,6 +338,34 @@ static cudaError_t schedule_prepare(RenderSchedule* sch, const DevParams& P, uin
     return cudaGetLastError();
 }
 
+// Occupancy of the three render_kernel variants, per device (a process may hold scenes on several GPUs, and handles
+// may be driven from several host threads): which = 0 plain, 1 with the dispatch-order hint, 2 counting.
+static cudaError_t render_occupancy(int which, int* n_sm, int* per_sm) {
+    constexpr int kMaxDev = 64;
+    static std::mutex mu;
+    static int sm[kMaxDev], occ[kMaxDev][3];   // zero-initialised: 0 = not asked yet
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    std::lock_guard<std::mutex> lock(mu);
+    const bool cached = dev >= 0 && dev < kMaxDev && occ[dev][which] != 0;
+    if (!cached) {
+        int n = 0, b = 0;
+        if ((e = cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
+        e = which == 2   ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, render_kernel<true, false>, kBlock, 0)
+            : which == 1 ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, render_kernel<false, true>, kBlock, 0)
+                         : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, render_kernel<false, false>, kBlock, 0);
+        if (e != cudaSuccess) return e;
+        b = b > 0 ? b : 1;
+        if (dev < 0 || dev >= kMaxDev) { *n_sm = n; *per_sm = b; return cudaSuccess; }
+        sm[dev] = n;
+        occ[dev][which] = b;
+    }
+    *n_sm = sm[dev];
+    *per_sm = occ[dev][which];
+    return cudaSuccess;
+}
+
 // scratch = (n_rows_local*W + 2) u32 words: per-pixel accumulators followed by the 64-bit queue head.
 cudaError_t launch_render(const DevScene& sc, const DevParams& P, uint32_t* d_fb, int32_t* d_hit, uint32_t* d_scratch,
                           DevCounters* d_counters, cudaStream_t stream, RenderSchedule* sch) {
@@ -346,22 +376,6 @@ cudaError_t launch_render(const DevScene& sc, const DevParams& P, uint32_t* d_fb
     const size_t head = (npix + 1) & ~(size_t)1;  // 8-byte aligned
     cudaError_t e = cudaMemsetAsync(d_scratch, 0, (head + 2) * sizeof(uint32_t), stream);
     if (e != cudaSuccess) return e;
-    static int blocks_per_sm[2] = {0, 0};
-    static int n_sm = 0;
-    const int which = d_counters ? 1 : 0;
-    if (!blocks_per_sm[which]) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
-        int b = 0;
-        e = d_counters ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, render_kernel<true, false>, kBlock, 0)
-                       : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, render_kernel<false, true>, kBlock, 0);
-        if (e != cudaSuccess) return e;
-        blocks_per_sm[which] = b > 0 ? b : 1;
-    }
-    unsigned long long want = (total + kBlock - 1) / kBlock;
-    const unsigned long long resident = (unsigned long long)n_sm * blocks_per_sm[which];
-    const unsigned grid = (unsigned)(want < resident ? want : resident);  // persistent: one wave
     unsigned long long* next = reinterpret_cast<unsigned long long*>(d_scratch + head);
     const uint32_t n_blocks = (uint32_t)tiles_x * (uint32_t)tiles_y;
     bool hint = sch && sch->enabled && !d_counters && RRT_REFILL_MIN == 32 && n_blocks >= sch->min_blocks;
@@ -376,6 +390,12 @@ cudaError_t launch_render(const DevScene& sc, const DevParams& P, uint32_t* d_fb
         sch->enabled = false;
         hint = false;
     }
+    // persistent grid: one wave of the variant about to be launched, on the device that launches it
+    int n_sm = 0, per_sm = 0;
+    if ((e = render_occupancy(d_counters ? 2 : (hint ? 1 : 0), &n_sm, &per_sm)) != cudaSuccess) return e;
+    const unsigned long long want = (total + kBlock - 1) / kBlock;
+    const unsigned long long resident = (unsigned long long)n_sm * per_sm;
+    const unsigned grid = (unsigned)(want < resident ? want : resident);
     const uint32_t* order = hint && sch->valid ? sch->order : nullptr;
     uint32_t* cost = hint ? sch->cost : nullptr;
     unsigned long long* stats = hint ? sch->stats + 2 * (sch->parity & 1) : nullptr;

@@ -49,76 +49,59 @@ class _DevFrame:
         self.__cuda_array_interface__ = {"shape": (height, width), "typestr": "<i4", "data": (ptr, False), "version": 2}
 
 
-class ShardedRenderer:
-    """Per-rank renderer: owns a replicated device scene and renders its interleaved tile rows.
+class HostFrame:
+    """One canvas in host memory shared by the ranks of a node (include/rrt.h, rrt_host_frame_*): a POSIX
+    shared-memory segment every rank maps and page-locks, with a process-shared barrier in its header."""
 
-    assemble="nccl": compact rows, one all-gather + de-interleave, the full frame on EVERY rank.
-    assemble="peer": fused render + gather — rank 0 owns the frame (rrt_frame_alloc), the other ranks map it
-        through CUDA IPC and their render kernels store finished pixels straight into it over NVLink; the
-        only collective left is a 4-byte all-reduce that orders "all kernels done" on the streams.
-    """
-
-    def __init__(self, ray_tracer, width, height, rank, world, tile_rows=DEFAULT_TILE_ROWS, group=None,
-                 assemble="nccl"):
-        import torch
-        self.rt, self.W, self.H = ray_tracer, width, height
-        self.rank, self.world, self.T = rank, world, tile_rows
-        self.group = group
-        self.mode = assemble if world > 1 else "nccl"
-        self.shard = abi.Shard(tile_rows, world, rank)
-        self.n_local = int(abi.lib().rrt_shard_rows(height, C.byref(self.shard)))
-        self.rpb = rows_per_block(height, tile_rows, world)
-        dev = torch.device("cuda", ray_tracer.device)
-        self.device = dev
-        self._own_frame = self._peer_frame = None
-        if self.mode == "peer":
-            self._setup_peer_frame()
-            return
-        self.local = torch.zeros((self.rpb, width), dtype=torch.int32, device=dev)     # u32 payload
-        self.gathered = torch.zeros((world, self.rpb, width), dtype=torch.int32, device=dev) if world > 1 else None
-        self.frame = torch.zeros((height, width), dtype=torch.int32, device=dev)
-
-    def _setup_peer_frame(self):
-        import torch
-        import torch.distributed as dist
+    def __init__(self, name, width, height, n_ranks, create, device=None, timeout=60.0):
         L = abi.lib()
-        handle = (C.c_ubyte * 64)()
-        if self.rank == 0:
-            p = C.c_void_p()
-            abi.check(L.rrt_frame_alloc(self.rt.device, self.W, self.H, C.byref(p)))
-            self._own_frame = p.value
-            abi.check(L.rrt_ipc_get_handle(self.rt.device, p, handle))
-        box = [bytes(handle)]
-        dist.broadcast_object_list(box, src=0, group=self.group)
-        if self.rank == 0:
-            self.dest = self._own_frame
-            self.frame = torch.as_tensor(_DevFrame(self.dest, self.H, self.W), device=self.device)
+        h = C.c_void_p()
+        if create:
+            abi.check(L.rrt_host_frame_create(name.encode(), width, height, n_ranks, C.byref(h)))
         else:
-            q = C.c_void_p()
-            buf = (C.c_ubyte * 64).from_buffer_copy(box[0])
-            abi.check(L.rrt_ipc_open_handle(self.rt.device, buf, C.byref(q)))
-            self._peer_frame = q.value
-            self.dest = q.value
-            self.frame = None
-        self._token = torch.zeros(1, dtype=torch.int32, device=self.device)
+            abi.check(L.rrt_host_frame_open(name.encode(), float(timeout), C.byref(h)))
+        self._h, self.name, self.W, self.H = h, name, width, height
+        if device is not None:
+            abi.check(L.rrt_host_frame_pin(h, device))
+        self.ptr = L.rrt_host_frame_pixels(h)
+        buf = (C.c_uint32 * (width * height)).from_address(self.ptr)
+        self.pixels = np.frombuffer(buf, dtype=np.uint32).reshape(height, width)
+
+    def barrier(self, timeout=120.0):
+        abi.check(abi.lib().rrt_host_frame_barrier(self._h, float(timeout)))
 
     def close(self):
         L = abi.lib()
-        if self._peer_frame:
-            L.rrt_ipc_close_handle(self.rt.device, C.c_void_p(self._peer_frame))
-            self._peer_frame = None
-        if self._own_frame:
+        for q in self._peer_frames:
+            L.rrt_ipc_close_handle(self.rt.device, C.c_void_p(q))
+        self._peer_frames = []
+        if self._own_frames:
             self.frame = None
-            L.rrt_frame_free(self.rt.device, C.c_void_p(self._own_frame))
-            self._own_frame = None
+            self._frames = [None, None]
+            for p in self._own_frames:
+                L.rrt_frame_free(self.rt.device, C.c_void_p(p))
+            self._own_frames = []
+        if self._host is not None:
+            self.frame = None
+            self._host.close()
+            self._host = None
 
     def render(self, params, stream=None):
-        """Enqueue this rank's share of Scene::draw_scene on `stream` (torch stream or None)."""
+        """Enqueue this rank's share of Scene::draw_scene on `stream` (torch stream or None = current)."""
         import torch
         s = stream or torch.cuda.current_stream(self.device)
         if self.mode == "peer":
+            self._cur = self._k & 1
+            self._k += 1
             abi.check(abi.lib().rrt_render_device_into_frame(self.rt.handle, C.byref(params), C.byref(self.shard),
-                                                             C.c_void_p(self.dest), C.c_void_p(s.cuda_stream)))
+                                                             C.c_void_p(self._dest[self._cur]), C.c_void_p(s.cuda_stream)))
+            return
+        if self.mode == "host":
+            if self._outstanding and self.world > 1:
+                self._host.barrier()          # rank 0 has finished reading the previous frame
+            self._outstanding = False
+            abi.check(abi.lib().rrt_render_to_host_frame(self.rt.handle, C.byref(params), C.byref(self.shard),
+                                                         C.c_void_p(self._host.ptr), C.c_void_p(s.cuda_stream)))
             return
         out = self.local if self.world > 1 else self.frame
         abi.check(abi.lib().rrt_render_device(self.rt.handle, C.byref(params), C.byref(self.shard),
@@ -126,16 +109,26 @@ class ShardedRenderer:
 
     def assemble(self, stream=None):
         """nccl: all-gather the compact shards and scatter them into the reference frame layout.
-        peer: the pixels are already in rank 0's frame; order every rank's kernel before what follows."""
+        peer: the pixels are already in rank 0's frame; order every rank's kernel before what follows on `stream`.
+        host: wait for this rank's copies, then for every rank's ("frame complete"); returns the shared host frame."""
         import torch
         import torch.distributed as dist
+        s = stream or torch.cuda.current_stream(self.device)
+        if self.mode == "host":
+            s.synchronize()
+            if self.world > 1:
+                self._host.barrier()
+            self._outstanding = True
+            return self.frame
         if self.world == 1:
             return self.frame
         if self.mode == "peer":
-            dist.all_reduce(self._token, group=self.group)     # stream-ordered after each rank's render kernel
+            with torch.cuda.stream(s):
+                dist.all_reduce(self._token, group=self.group)     # stream-ordered after each rank's render kernel
+            self.frame = self._frames[self._cur]
             return self.frame
-        dist.all_gather_into_tensor(self.gathered, self.local, group=self.group)
-        s = stream or torch.cuda.current_stream(self.device)
+        with torch.cuda.stream(s):
+            dist.all_gather_into_tensor(self.gathered, self.local, group=self.group)
         abi.check(abi.lib().rrt_deinterleave_device(self.rt.device, self.gathered.data_ptr(), self.rpb, self.W,
                                                     self.H, self.T, self.world, self.frame.data_ptr(),
                                                     C.c_void_p(s.cuda_stream)))

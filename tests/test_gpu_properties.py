@@ -279,3 +279,15 @@ def test_frame_parallel_sequence_world1(rrt, scenes):
     for i, c in enumerate(cams):
         assert np.array_equal(seq[i], sc.draw_scene(rt, **c))
     rt.close()
+
+
+def test_max_depth_beyond_the_mirror_stack_is_refused(rrt, scenes):
+    # the reference recurses to any depth (raytracer.rs:76); the kernel keeps 16 mirror levels per lane: a deeper
+    # request must fail loudly (RRT_ERR_INVALID), never render a different image with RRT_OK
+    rt = rrt.RayTracer(scenes("model2"))
+    sc = rrt.Scene(32, 16)
+    sc.draw_scene(rt, max_depth=16)
+    with pytest.raises(Exception) as ei:
+        sc.draw_scene(rt, max_depth=17)
+    assert "max_depth" in str(ei.value)
+    rt.close()

@@ -36,3 +36,9 @@ build s_gfilter_prim -DRRT_SHADOW_FILTER=2 -DRRT_PRIMARY_FILTER=1
 build t_gfilter_all -DRRT_SHADOW_FILTER=2 -DRRT_PRIMARY_FILTER=1 -DRRT_SLAB_PRED=1 -DRRT_LATE_PRUNE=1 -DRRT_CULL_LOOP=3 -DRRT_PEND=2
 build u_sparse      -DRRT_SHADOW_FILTER=2 -DRRT_SPARSE_PRIMARY=1
 build v_sparse_all  -DRRT_SHADOW_FILTER=2 -DRRT_SPARSE_PRIMARY=1 -DRRT_SLAB_PRED=1 -DRRT_LATE_PRUNE=1 -DRRT_CULL_LOOP=3 -DRRT_PEND=2
+# register budget at today's code size (the 128 x 8 = 64-register choice dates from kernel v3)
+build w_mb6         -DRRT_MIN_BLOCKS=6
+build x_mb5         -DRRT_MIN_BLOCKS=5
+build y_gfilter_mb6 -DRRT_SHADOW_FILTER=2 -DRRT_MIN_BLOCKS=6
+build z_sparse_all_mb6 -DRRT_SHADOW_FILTER=2 -DRRT_SPARSE_PRIMARY=1 -DRRT_SLAB_PRED=1 -DRRT_LATE_PRUNE=1 -DRRT_CULL_LOOP=3 -DRRT_PEND=2 -DRRT_MIN_BLOCKS=6
+build z_sparse_all_mb5 -DRRT_SHADOW_FILTER=2 -DRRT_SPARSE_PRIMARY=1 -DRRT_SLAB_PRED=1 -DRRT_LATE_PRUNE=1 -DRRT_CULL_LOOP=3 -DRRT_PEND=2 -DRRT_MIN_BLOCKS=5
