@@ -5,13 +5,18 @@
   python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
 
 A "step" = one frame of the workload (Scene::draw_scene, engine.rs:186-255): at N GPUs the frame is
-sharded by interleaved tile rows (no data-path collective), then one NCCL all-gather + de-interleave
-assembles it on every rank.  Default workload = BASELINE.json configs[3] (the 1M-triangle sphere grid at
+sharded by interleaved tile rows (no data-path collective).  `value` is device-timed with the frame left in
+device memory (N>1: the render kernels store their pixels into rank 0's frame over NVLink); `e2e` ends with the
+frame in HOST memory, the reference's Canvas.buffer (N>1: every rank copies its rows over its own PCIe link into
+one shared page-locked frame).  Default workload = BASELINE.json configs[3] (the 1M-triangle sphere grid at
 3840x2160 that the metric's 1/2/4/8-GPU scaling and the >=1000x target are quoted on); the other
-configs are parity-test cases, selectable with --workload.  Prints ONE JSON line on rank 0.
+configs are parity-test cases, selectable with --workload.  Prints ONE JSON line on rank 0, with a `parity`
+block: the benchmarked frame against the CPU oracle on a pixel lattice, and a digest of the assembled frame
+that must be the same at every N.
 """
 import argparse
 import ctypes as C
+import hashlib
 import json
 import os
 import statistics
@@ -113,14 +118,14 @@ def cpu_baseline(sd, params, target_seconds=15.0, threads=0):
     total = 4.0 * W * (H - 1)
     frac = min(1.0, want / total)
     step = max(1, int(round((1.0 / frac) ** 0.5)))
-    _, _, sec, cnt = osc.render(params, want_hit_ids=False, n_threads=cores, row_step=step, col_step=step, counters=True)
+    ofb, ohit, sec, cnt = osc.render(params, want_hit_ids=True, n_threads=cores, row_step=step, col_step=step, counters=True)
     rays = cnt["rays_primary"]
     per_ray = {k: cnt[k] / rays for k in ("n_a", "n_u", "n_v", "n_t", "n_slab", "n_node", "rays_shadow", "rays_reflect")}
     osc.close()
     return {"value": rays / sec / 1e6, "unit": "Mrays/s", "cores": cores, "kind": "port",
             "sample": f"every {step}th row x every {step}th column of the {W}x{H} frame = {rays} primary rays in {sec:.2f} s "
                       f"(OpenMP dynamic over rows, all {cores} host threads)",
-            "seconds": sec, "rays": rays}, per_ray
+            "seconds": sec, "rays": rays, "lattice": (step, ofb, ohit)}, per_ray
 
 
 def algorithmic_work(per_ray):
@@ -157,6 +162,20 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
+def frame_digest(frame_u32):
+    """64-bit digest of a frame in the reference canvas layout (little-endian u32 words, row-major)."""
+    import numpy as np
+    return hashlib.blake2b(np.ascontiguousarray(frame_u32, dtype="<u4").tobytes(), digest_size=8).hexdigest()
+
+
+def kernel_id():
+    """Identifies the device code that is running: sha1 over the kernel sources + build flags (written by build.py)."""
+    try:
+        return open(os.path.join(ROOT, "rust-ray-tracer_b200", "csrc", "librrt_b200.kernel_id")).read().strip()
+    except OSError:
+        return None
+
+
 def run_gpu(args):
     import numpy as np
     import torch
@@ -170,7 +189,8 @@ def run_gpu(args):
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if world != args.gpus:
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch N>1 with torch.distributed.run")
-    if abi.lib().rrt_device_count() <= local_rank:
+    L = abi.lib()
+    if L.rrt_device_count() <= local_rank:
         raise SystemExit("no CUDA device for this rank: the renderer has no CPU fallback")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
@@ -193,6 +213,7 @@ def run_gpu(args):
     stats = rt.stats()
     p = rt.params(W, H)
     sr = ShardedRenderer(rt, W, H, rank, world, tile_rows=DEFAULT_TILE_ROWS, assemble=args.assemble)
+    sr_host = ShardedRenderer(rt, W, H, rank, world, tile_rows=DEFAULT_TILE_ROWS, assemble="host")
     flush = torch.empty(256 << 20, dtype=torch.int8, device=dev)      # > 126 MB L2
     stream = torch.cuda.current_stream(dev)
     K, Wm = args.steps, args.warmup
@@ -231,6 +252,15 @@ def run_gpu(args):
         sr.render(step_params())
         sr.assemble()
 
+    # ---- the first frame a handle ever renders at this shape: raster dispatch order, both searches switched on
+    # (Scene::draw_scene is a one-shot call in the reference, src/main.rs:73-76).  A 64x64 frame first, so that loading
+    # the module is not in the number.
+    small = rrt_b200.Scene(64, 64)
+    small.draw_scene(rt)
+    if stats.get("n_cull_nodes") and os.environ.get("RRT_SEARCH_MODE", "1") == "1":
+        abi.check(L.rrt_scene_search_mode(rt.handle, 1, 0, 0))     # as a fresh handle: both searches on, nothing decided yet
+    first_ms = timed_steps(1, frame)
+    step_no[0] = 0
     for _ in range(Wm):
         frame()
     sampler = ClockSampler(local_rank)
@@ -242,8 +272,25 @@ def run_gpu(args):
     # dominant kernel alone (render_kernel on this rank's shard), same hygiene
     step_no[0] = 0
     kern_ms = timed_steps(K, lambda: sr.render(step_params())) / K
+    search_state = (C.c_uint32 * 12)()
+    abi.check(L.rrt_scene_search_state(rt.handle, search_state))
 
-    # ---- end to end through the public API with HOST buffers (pinned), copies inside the timed region
+    # the same K frames without the dispatch-order hint (every frame in raster order, as a first frame is)
+    abi.check(L.rrt_scene_order_hint(rt.handle, 0))
+    step_no[0] = 0
+    for _ in range(2):
+        frame()
+    step_no[0] = 0
+    nohint_ms = timed_steps(K, frame) / K
+    abi.check(L.rrt_scene_order_hint(rt.handle, 1))
+    step_no[0] = 0
+    for _ in range(2):
+        frame()
+
+    # ---- end to end through the public API with HOST buffers, copies inside the timed region.
+    # N = 1: Scene.draw_scene -> rrt_render (params H2D as kernel arguments, kernel, frame D2H into pinned memory).
+    # N > 1: every rank renders its rows and copies them over its own PCIe link into ONE shared page-locked host frame
+    # (rrt_render_to_host_frame + rrt_host_frame_barrier): the frame is complete in host memory when the step ends.
     host = torch.empty((H, W), dtype=torch.int32, pin_memory=True)
     host_np = host.numpy().view(np.uint32).reshape(-1)
     scene = rrt_b200.Scene(W, H)
@@ -256,12 +303,10 @@ def run_gpu(args):
                 step_no[0] += 1
                 scene.draw_scene(rt, origin=origin, camera_rot=rot)
             else:
-                scene.draw_scene(rt)           # rrt_render: params H2D (kernel args) + kernel + frame D2H
+                scene.draw_scene(rt)
         else:
-            frame()
-            if rank == 0:
-                host.copy_(sr.frame, non_blocking=True)
-            torch.cuda.synchronize(dev)
+            sr_host.render(step_params())
+            sr_host.assemble()
 
     step_no[0] = 0 if Wm >= 1 else 1       # c5: walk the same orbit frames as the device-timed leg (warm-up, then K)
     for _ in range(max(1, Wm)):
@@ -277,87 +322,140 @@ def run_gpu(args):
     e2e_val = rays_frame * K / (float(e2e_ms.item()) * 1e-3) / 1e6
     clocks = sampler.stop() if rank == 0 else None
 
+    # ---- parity of the benchmarked workload (outside every timed region): one designated frame (c5: orbit frame 5)
+    # through BOTH assembly paths used above, read on rank 0
+    pk = {}
+    if args.workload == "c5":
+        origin, rot = rrt_b200.orbit_camera(5)
+        pk = dict(origin=origin, camera_rot=rot)
+    pp = rt.params(W, H, **pk)
+    sr.render(pp)
+    dev_frame = sr.assemble()
+    sync_all()
+    frame_dev = dev_frame.cpu().numpy().view(np.uint32).copy() if rank == 0 else None
+    sr_host.render(pp)
+    host_frame = sr_host.assemble()
+    frame_host = np.array(host_frame, dtype=np.uint32, copy=True) if rank == 0 else None
+    if world > 1:
+        dist.barrier()
+
     if rank == 0:
         # executed work of OUR kernel (instrumented build of the same kernel), whole frame
         cnt = abi.Counters()
-        abi.check(abi.lib().rrt_render_counters(rt.handle, C.byref(p), None, C.byref(cnt)))
+        abi.check(L.rrt_render_counters(rt.handle, C.byref(p), None, C.byref(cnt)))
         cd = cnt.as_dict()
         executed = {k + "_per_ray": cd[k] / cd["rays_primary"] for k in ("mt_tests", "cull_tests", "box_tests", "nodes_entered", "rays_shadow", "rays_reflect")}
         fp64 = C.c_double(0.0)
-        abi.check(abi.lib().rrt_microbench_fp64(local_rank, C.byref(fp64), None))
+        abi.check(L.rrt_microbench_fp64(local_rank, C.byref(fp64), None))
         peaks = {}
         try:
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
         except OSError:
             pass
         hbm_peak, hbm_src = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
-        if world == 1:
-            cpu, per_ray = cpu_baseline(sd, p, target_seconds=args.cpu_seconds)
-        else:
-            cpu, per_ray = None, cpu_baseline(sd, p, target_seconds=2.0)[1]   # counters only
+        cpu, per_ray = cpu_baseline(sd, pp, target_seconds=args.cpu_seconds if world == 1 else 4.0)
+        # ---- parity block: this run's frame against the oracle's lattice of the same frame
+        step, ofb, ohit = cpu["lattice"]
+        rows, cols = np.arange(1, H, step), np.arange(0, W, step)
+        ix = np.ix_(rows, cols)
+        whole = rrt_b200.Scene(W, H)
+        fb1 = whole.draw_scene(rt, want_hit_ids=True, **pk).copy()          # single GPU, whole frame, with hit ids
+        sh = np.array([16, 8, 0])
+        rgb = lambda f: ((f[..., None] >> sh) & 255).astype(np.int32)
+        parity = {
+            "against": "oracle/ (CPU restatement of engine.rs:186-255 -> raytracer.rs:29-112), same scene and camera",
+            "lattice": f"every {step}th row x column of the {W}x{H} frame: {rows.size * cols.size} pixels, {4 * rows.size * cols.size} samples",
+            "hit_id_agreement": float((whole.hit_ids[ix] == ohit[ix]).mean()),
+            "max_rgb_diff": int(np.abs(rgb(frame_host[ix]) - rgb(ofb[ix])).max()),
+            "pixels_identical": bool(np.array_equal(frame_host[ix], ofb[ix])),
+            "row0_zero": bool((frame_host[0] == 0).all()),
+            "assembled_equals_single_gpu_frame": bool(np.array_equal(frame_host, fb1) and np.array_equal(frame_dev, fb1)),
+            "frame_digest": frame_digest(frame_host),
+            "note": "frame_digest = blake2b-64 of the frame assembled in host memory by this run's e2e path; equal at every N",
+        }
         flops_ray, bytes_ray = algorithmic_work(per_ray)
         rays_launch = 4 * W * sr.n_local
-        traffic, prof = None, {}
+        prof = {}
         try:
             prof = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
-            traffic = prof.get(args.workload)
         except OSError:
             pass
-        a_tf = flops_ray * rays_launch / (kern_ms * 1e-3) / 1e12
-        a_gb = bytes_ray * rays_launch / (kern_ms * 1e-3) / 1e9
+        w = args.workload
+        kid = kernel_id()
+        have_prof = world == 1 and (w + "_fp64_lane_inst") in prof
+        lane_inst = prof.get(w + "_fp64_lane_inst")
+        traffic = prof.get(w)
         order_hint = os.environ.get("RRT_ORDER_HINT", "1") != "0"
+        a_lane = lane_inst / (kern_ms * 1e-3) / 1e12 if have_prof else None
         line = {
             "metric": "Mrays/s (primary rays, 4 per pixel)", "value": value, "unit": "Mrays/s", "n_gpus": world,
             "steps": K, "warmup": Wm, "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"{args.workload}: {desc} at {W}x{H}", "n_tris": int(sd.n_tris),
-                       "parallelism": (f"interleaved tile rows x{world} (tile_rows={DEFAULT_TILE_ROWS}), scene replicated, " +
-                                       ("render kernels store finished pixels into rank 0's frame over NVLink peer memory"
-                                        if sr.mode == "peer" else "NCCL all-gather + de-interleave per frame"))
-                       if world > 1 else "single GPU",
-                       "l2": "flushed (256 MB write) between timed iterations", "octree": stats,
-                       "dispatch_order": ("raster order for the first frame of a shape; afterwards the last part of the frame's "
-                                          "16x4-pixel blocks is handed out heaviest first, by the cost measured while rendering "
-                                          "the previous frame (sorted on a side stream; every sample is traced in full every "
-                                          "frame, results bit-identical with RRT_ORDER_HINT=0)") if order_hint else "raster order",
-                       "scene_build_s": round(build_s, 2)},
+            "config": {"workload": f"{args.workload}: {desc} at {W}x{H}", "n_tris": int(sd.n_tris)},
+            "details": {
+                "parallelism": (f"interleaved tile rows x{world} (tile_rows={DEFAULT_TILE_ROWS}), scene replicated; device-timed value: " +
+                                ("render kernels store finished pixels into rank 0's frame over NVLink peer memory (two frames used alternately)"
+                                 if sr.mode == "peer" else "NCCL all-gather + de-interleave per frame") +
+                                "; e2e: every rank copies its rows device->host into one shared page-locked frame")
+                if world > 1 else "single GPU",
+                "l2": "flushed (256 MB write) between timed iterations", "octree": stats,
+                "dispatch_order": ("raster order for the first frame of a shape; afterwards the last part of the frame's "
+                                   "16x4-pixel blocks is handed out heaviest first, by the cost measured while rendering "
+                                   "the previous frame") if order_hint else "raster order",
+                "searches": {"filter_on": int(search_state[2]), "sparse_on": int(search_state[6]),
+                             "shadow_queries_answered_handed": [int(search_state[8]), int(search_state[9])],
+                             "camera_rays_answered_handed": [int(search_state[10]), int(search_state[11])],
+                             "note": "state after the timed frames (rrt_scene_search_state); both paths are exact"},
+                "scene_build_s": round(build_s, 2), "kernel_id": kid},
             "clocks": clocks,
             "e2e": {"value": e2e_val, "unit": "Mrays/s", "h2d_bytes_per_step": C.sizeof(abi.RenderParams),
-                    "d2h_bytes_per_step": W * H * 4, "ms_per_step": float(e2e_ms.item()) / K},
-            # own kernels per step: render_kernel (+ order_stats_kernel, order_keys_kernel of the dispatch-order hint;
-            # the cub radix-sort kernels behind them are library code and not counted) (+ de-interleave after NCCL)
-            "gpu_launches": K * ((3 if order_hint else 1) + (1 if world > 1 and sr.mode == "nccl" else 0)),
-            "roofline": {"bound": "fp64", "kernel": "render_kernel", "achieved": a_tf, "peak": fp64.value,
-                         "unit": "TFLOP/s", "frac": a_tf / fp64.value, "traffic": traffic,
-                         "note": "achieved = REFERENCE-executed flops/ray (SURVEY 8d formula, oracle counters) x rays per launch / "
-                                 "kernel time; peak = FP64 DMUL+DADD without FMA measured live (rrt_microbench_fp64). The kernel skips "
-                                 "most of that work through conservative culling, so frac may exceed 1; executed work below.",
-                         "kernel_ms": kern_ms, "algorithmic_flops_per_ray": flops_ray, "algorithmic_bytes_per_ray": bytes_ray,
-                         "reference_work_per_ray": per_ray, "executed_per_ray": executed},
-            # what the kernel itself pushes through the FP64 pipe (ncu opcode counts of the committed profile of
-            # this workload, whole launch on one GPU) over the live kernel time, against the same measured peak
-            "executed_fp64": (None if world != 1 or (args.workload + "_fp64_lane_inst") not in prof else {
-                "lane_inst_per_launch": prof[args.workload + "_fp64_lane_inst"],
-                "achieved": prof[args.workload + "_fp64_lane_inst"] / (kern_ms * 1e-3) / 1e12, "peak": fp64.value,
-                "unit": "T lane-inst/s (DADD/DMUL/DFMA/DSETP, one per lane)",
-                "frac": prof[args.workload + "_fp64_lane_inst"] / (kern_ms * 1e-3) / 1e12 / fp64.value,
-                "issue_active_pct": prof.get(args.workload + "_issue_active_pct"),
-                "fp64_pipe_active_pct": prof.get(args.workload + "_fp64_pipe_active_pct"),
-                "source": "profiles/traffic.json"}),
-            "roofline_hbm": {"bound": "hbm", "achieved": a_gb, "peak": hbm_peak, "unit": "GB/s", "frac": a_gb / hbm_peak,
-                             "peak_source": hbm_src, "traffic": traffic,
-                             "note": "algorithmic bytes are cache-level (scene is L2-resident); not the limiter"},
+                    "d2h_bytes_per_step": W * H * 4, "ms_per_step": float(e2e_ms.item()) / K,
+                    "path": "Scene.draw_scene -> rrt_render (pinned host canvas)" if world == 1 else
+                            "ShardedRenderer(assemble='host'): rrt_render_to_host_frame per rank + rrt_host_frame_barrier"},
+            # steady state vs what a one-shot caller sees: first frame of a handle at this shape (raster order, both searches
+            # tried), and the K timed frames again with the dispatch-order hint switched off
+            "first_frame_ms": first_ms, "ms_per_step_no_hint": nohint_ms,
+            # own kernels per step: render_kernel + search_switch_kernel (+ order_stats_kernel, order_keys_kernel of the
+            # dispatch-order hint; the cub radix-sort kernels behind them are library code and not counted)
+            "gpu_launches": K * ((4 if order_hint else 2) + (1 if world > 1 and sr.mode == "nccl" else 0)),
+            "parity": parity,
+            # The kernel is bound by the FP64 vector pipe and instruction issue, not by HBM (the scene is L2-resident):
+            # achieved = FP64-pipe lane instructions the kernel EXECUTES per launch (ncu opcode counts of the committed
+            # capture of this workload, profiles/traffic.json) / live kernel time; peak = DMUL+DADD without FMA measured live.
+            "roofline": {"bound": "fp64", "kernel": "render_kernel", "achieved": a_lane, "peak": fp64.value,
+                         "unit": "T FP64 lane-instructions/s (DADD/DMUL/DFMA/DSETP executed, one per active lane)",
+                         "frac": (a_lane / fp64.value) if have_prof else None,
+                         "traffic": traffic, "kernel_ms": kern_ms,
+                         "fp64_lane_inst_per_launch": lane_inst,
+                         "issue_active_pct": prof.get(w + "_issue_active_pct"),
+                         "fp64_pipe_active_pct": prof.get(w + "_fp64_pipe_active_pct"),
+                         "avg_active_lanes": prof.get(w + "_avg_active_lanes"),
+                         "dram_gbs": (traffic / (kern_ms * 1e-3) / 1e9) if (have_prof and traffic) else None,
+                         "dram_frac_of_measured_hbm": (traffic / (kern_ms * 1e-3) / 1e9 / hbm_peak) if (have_prof and traffic) else None,
+                         "hbm_peak_gbs": hbm_peak, "hbm_peak_source": hbm_src,
+                         "profile": {"source": prof.get(w + "_source"), "kernel_id": prof.get(w + "_kernel_id"),
+                                     "matches_this_build": bool(kid and prof.get(w + "_kernel_id") == kid)},
+                         "note": "N>1 and workloads without a committed capture: achieved/frac are null (never a guess)"},
+            # what the REFERENCE executes per primary ray (SURVEY 8d formula on the oracle's counters) against what this
+            # kernel executes: an algorithmic speed-up, NOT a roofline fraction
+            "algorithmic_speedup": {"reference_flops_per_ray": flops_ray, "reference_bytes_per_ray": bytes_ray,
+                                    "reference_work_per_ray": per_ray, "executed_per_ray": executed,
+                                    "reference_tflops_equivalent": flops_ray * rays_launch / (kern_ms * 1e-3) / 1e12},
         }
-        if cpu is not None:
+        if world == 1:
             line["cpu_baseline"] = {k: cpu[k] for k in ("value", "unit", "cores", "kind", "sample")}
         sys.stdout.flush()
         os.write(json_fd, (json.dumps(line) + "\n").encode())
-    if world > 1:                 # peers unmap rank 0's frame before rank 0 frees it
+    if world > 1:                 # peers unmap rank 0's frames before rank 0 frees them
         if rank != 0:
             sr.close()
+            sr_host.close()
         dist.barrier()
         if rank == 0:
             sr.close()
+            sr_host.close()
+    else:
+        sr_host.close()
     rt.close()
     if world > 1:
         dist.barrier()

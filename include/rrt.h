@@ -164,6 +164,20 @@ int rrt_scene_get_stats(const rrt_scene* scene, rrt_scene_stats* out);
  * on one stream at a time (they share the handle's scratch and this state). */
 int rrt_scene_order_hint(rrt_scene* scene, int enable);
 
+/* Searches that go round the octree walk (no counterpart in the reference; results are bit-identical in every mode).
+ * Scene creation also builds ONE culling hierarchy over all triangles of the scene; shadow queries first ask it whether
+ * any triangle is hit below max_t at all ("none" is exactly the reference's None), camera rays look for their closest
+ * triangle in it and answer themselves when the octree walk provably returns the same; every
+ * other ray, and every ray a search cannot decide, takes the exact walk of ray.rs:104-168.
+ * mode 0: walk only; 1 (default): each search is switched on / off per scene handle from one frame to the next by how
+ * many of its rays it answered; 2: always tried; 3: switched as given here (filter_on / sparse_on).  RRT_SEARCH_MODE in
+ * the environment at scene creation sets the initial mode (0 also skips building the hierarchy).
+ * rrt_scene_search_state (synchronises the device): out[2] filter switch, out[6] sparse switch, out[3] frames decided,
+ * out[8..9] shadow queries the filter answered / handed to the walk in the last decided frame, out[10..11] camera rays
+ * likewise (mode 1 only; out[0..1], out[4..5] are the running counts of a frame in flight). */
+int rrt_scene_search_mode(rrt_scene* scene, int mode, int filter_on, int sparse_on);
+int rrt_scene_search_state(rrt_scene* scene, uint32_t out[12]);
+
 /* ---- rendering (replaces Scene::draw_scene, engine.rs:186-255) ---- */
 /* Host-buffer call: fb_0rgb[width*height] receives the reference canvas layout
  * (0x00RRGGBB, row-major, top row first, row 0 left zero: engine.rs:146-158, entities.rs:32-36).

@@ -52,6 +52,14 @@ def build(force=False, verbose=False):
     if r.returncode != 0:
         sys.stderr.write(log)
         raise RuntimeError("nvcc failed")
+    # what device code this library holds: sha1 over the kernel sources and the flags they were compiled with
+    # (bench.py reports it next to the kernel id of the committed ncu capture it takes its roofline counts from)
+    import hashlib
+    h = hashlib.sha1(" ".join(NVCC_FLAGS + os.environ.get("RRT_EXTRA_FLAGS", "").split()).encode())
+    for f in ["rrt_render.cu", "rrt_device.cuh", "rrt_trace.cuh", "rrt_shade.cuh", "rrt_raygen.cuh", "rrt_octree.h"]:
+        h.update(open(os.path.join(CSRC, f), "rb").read())
+    with open(OUT[:-3] + ".kernel_id", "w") as f:
+        f.write(h.hexdigest()[:16] + "\n")
     if verbose:
         print(log)
     return OUT

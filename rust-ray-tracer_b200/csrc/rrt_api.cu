@@ -67,6 +67,8 @@ struct rrt_scene {
     size_t fb_cap = 0, hit_cap = 0, scratch_cap = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     RenderSchedule sched;            // dispatch order of the next frame from the measured cost of this one (rrt_render.h)
+    uint32_t* d_fstat = nullptr;     // what the searches round the walk returned last frame + their switches (DevParams::fstat)
+    int search_mode = 1;             // RRT_SEARCH_MODE at scene creation: 0 walk only, 1 switched per frame (default), 2 always
     // rrt_render_frames: two device frames, a render and a copy stream, created on first use
     uint32_t* d_seq_fb[2] = {nullptr, nullptr};
     size_t seq_cap[2] = {0, 0};
@@ -90,6 +92,7 @@ struct rrt_scene {
         if (d_fb) cudaFree(d_fb);
         if (d_hit) cudaFree(d_hit);
         if (d_scratch) cudaFree(d_scratch);
+        if (d_fstat) cudaFree(d_fstat);
         sched.release();
         if (seq_render) { cudaStreamSynchronize(seq_render); cudaStreamDestroy(seq_render); }
         if (seq_copy) { cudaStreamSynchronize(seq_copy); cudaStreamDestroy(seq_copy); }
@@ -107,7 +110,7 @@ struct rrt_scene {
 
 namespace {
 
-int make_params(const rrt_render_params* p, const rrt_shard* sh, DevParams* out) {
+int make_params(const rrt_scene* scene, const rrt_render_params* p, const rrt_shard* sh, DevParams* out) {
     if (!p) return fail(RRT_ERR_INVALID, "null params");
     if (p->width <= 0 || p->height <= 0) return fail(RRT_ERR_INVALID, "width/height must be positive");
     if ((int64_t)p->width * p->height > (int64_t)1 << 30) return fail(RRT_ERR_INVALID, "frame too large");
@@ -141,11 +144,9 @@ int make_params(const rrt_render_params* p, const rrt_shard* sh, DevParams* out)
     d.n_shards = sh->n_shards;
     d.shard_index = sh->shard_index;
     d.n_rows_local = rrt_shard_rows(p->height, sh);
-    // experiment builds (-DRRT_SHADOW_FILTER=1) only: RRT_SHADOW_FILTER_RT = 0 no filter, 1 (default) switched from one
-    // launch to the next by what the filtered queries returned (rrt_render.cu), 2 always on — same library, same frames
-    const char* sf = std::getenv("RRT_SHADOW_FILTER_RT");
-    const int sfm = sf ? std::atoi(sf) : 1;
-    d.shadow_filter = sfm < 0 || sfm > 2 ? 1 : sfm;
+    d.search_mode = scene ? scene->search_mode : 0;
+    d.fstat = scene ? scene->d_fstat : nullptr;
+    if (!d.fstat && d.search_mode == 1) d.search_mode = 0;
     *out = d;
     return RRT_OK;
 }
@@ -227,9 +228,15 @@ int rrt_scene_create(const rrt_scene_desc* d, int device, rrt_scene** out) {
     std::string err;
     if (!build_tree(tree, d->v, d->n_tris, d->root_min, d->root_max, &err)) return fail(RRT_ERR_DEPTH, err);
     FlatScene flat;
-    flatten(tree, d->v, cull_threshold(), cull_leaf(), &flat);
+    // RRT_SEARCH_MODE: 0 = octree walk only (no scene-wide hierarchy is built), 1 = the searches that go round the walk
+    // are switched per frame by what they answered (default), 2 = always tried
+    int search_mode = 1;
+    if (const char* e = std::getenv("RRT_SEARCH_MODE")) search_mode = std::max(0, std::min(2, std::atoi(e)));
+    flatten(tree, d->v, cull_threshold(), cull_leaf(), &flat, search_mode != 0);
+    if (flat.global_root == 0u) search_mode = 0;
 
     auto sc = std::make_unique<rrt_scene>();
+    sc->search_mode = search_mode;
     sc->device = device;
     if (const char* e = getenv("RRT_ORDER_HINT")) sc->sched.enabled = atoi(e) != 0;
     if (const char* e = getenv("RRT_ORDER_TAIL")) sc->sched.tail_safety = (float)atof(e);   // tuning knob (rrt_render.h)
@@ -253,6 +260,13 @@ int rrt_scene_create(const rrt_scene_desc* d, int device, rrt_scene** out) {
     sc->dev.n_nodes = (uint32_t)flat.nodes.size();
     sc->dev.root_tri_count = st.n_tris_stored ? 1u : 0u;
     sc->dev.planes_safe = (flat.planes_safe && !std::getenv("RRT_SLOW_DIV")) ? 1u : 0u;
+    sc->dev.global_root = flat.global_root;
+    sc->dev.sparse_ok = flat.sparse_ok ? 1u : 0u;
+    {
+        const uint32_t init[12] = {0u, 0u, 1u, 0u, 0u, 0u, 1u, 0u, 0u, 0u, 0u, 0u};   // both searches start switched on
+        CU(cudaMalloc((void**)&sc->d_fstat, sizeof init));
+        CU(cudaMemcpy(sc->d_fstat, init, sizeof init, cudaMemcpyHostToDevice));
+    }
 #if RRT_CULL_F32
     sc->dev.cull_o_max = kCullOriginRel * flat.scale;
 #else
@@ -312,6 +326,26 @@ int rrt_scene_order_hint(rrt_scene* s, int enable) {
     return RRT_OK;
 }
 
+int rrt_scene_search_mode(rrt_scene* s, int mode, int filter_on, int sparse_on) {
+    if (!s) return fail(RRT_ERR_INVALID, "null scene");
+    if (mode < 0 || mode > 3) return fail(RRT_ERR_INVALID, "search mode must be 0..3");
+    if (mode != 0 && s->dev.global_root == 0u)
+        return fail(RRT_ERR_INVALID, "scene was created without the scene-wide hierarchy (RRT_SEARCH_MODE=0 or a scene it does not apply to)");
+    CU(cudaSetDevice(s->device));
+    const uint32_t init[12] = {0u, 0u, mode == 3 ? (filter_on ? 1u : 0u) : 1u, 0u, 0u, 0u, mode == 3 ? (sparse_on ? 1u : 0u) : 1u, 0u, 0u, 0u, 0u, 0u};
+    CU(cudaMemcpy(s->d_fstat, init, sizeof init, cudaMemcpyHostToDevice));
+    s->search_mode = mode;
+    return RRT_OK;
+}
+
+int rrt_scene_search_state(rrt_scene* s, uint32_t out[12]) {
+    if (!s || !out) return fail(RRT_ERR_INVALID, "null argument");
+    CU(cudaSetDevice(s->device));
+    CU(cudaDeviceSynchronize());
+    CU(cudaMemcpy(out, s->d_fstat, 12 * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+    return RRT_OK;
+}
+
 int rrt_scene_get_stats(const rrt_scene* s, rrt_scene_stats* out) {
     if (!s || !out) return fail(RRT_ERR_INVALID, "null argument");
     *out = s->stats;
@@ -351,7 +385,7 @@ int rrt_render_device(rrt_scene* s, const rrt_render_params* p, const rrt_shard*
                       int32_t* d_hit_ids, void* cuda_stream) {
     if (!s || !d_fb) return fail(RRT_ERR_INVALID, "null argument");
     DevParams P;
-    int rc = make_params(p, shard, &P);
+    int rc = make_params(s, p, shard, &P);
     if (rc) return rc;
     CU(cudaSetDevice(s->device));
     if ((rc = ensure(&s->d_scratch, &s->scratch_cap, render_scratch_words(P.n_rows_local, P.W)))) return rc;
@@ -363,7 +397,7 @@ int rrt_render_device_into_frame(rrt_scene* s, const rrt_render_params* p, const
                                  void* cuda_stream) {
     if (!s || !d_frame) return fail(RRT_ERR_INVALID, "null argument");
     DevParams P;
-    int rc = make_params(p, shard, &P);
+    int rc = make_params(s, p, shard, &P);
     if (rc) return rc;
     P.full_frame = 1;
     CU(cudaSetDevice(s->device));
@@ -424,7 +458,7 @@ int rrt_render_to_host_frame(rrt_scene* s, const rrt_render_params* p, const rrt
                              void* cuda_stream) {
     if (!s || !host_frame) return fail(RRT_ERR_INVALID, "null argument");
     DevParams P;
-    int rc = make_params(p, shard, &P);
+    int rc = make_params(s, p, shard, &P);
     if (rc) return rc;
     CU(cudaSetDevice(s->device));
     cudaStream_t st = (cudaStream_t)cuda_stream;
@@ -446,7 +480,7 @@ int rrt_render_to_host_frame(rrt_scene* s, const rrt_render_params* p, const rrt
 int rrt_render(rrt_scene* s, const rrt_render_params* p, uint32_t* fb, int32_t* hit_ids, float* device_ms) {
     if (!s || !fb) return fail(RRT_ERR_INVALID, "null argument");
     DevParams P;
-    int rc = make_params(p, nullptr, &P);
+    int rc = make_params(s, p, nullptr, &P);
     if (rc) return rc;
     CU(cudaSetDevice(s->device));
     const size_t n = (size_t)P.W * P.H;
@@ -488,7 +522,7 @@ int rrt_render_frames(rrt_scene* s, const rrt_render_params* params, int32_t n_f
         CU(cudaEventRecord(s->seq_t0, s->seq_render));
         for (int32_t i = 0; i < n_frames; ++i) {
             DevParams P;
-            if ((rc = make_params(params + i, nullptr, &P))) return rc;
+            if ((rc = make_params(s, params + i, nullptr, &P))) return rc;
             const size_t n = (size_t)P.W * P.H;
             const int b = i & 1;
             if ((rc = ensure(&s->d_seq_fb[b], &s->seq_cap[b], n))) return rc;   // no-op after the first two frames
@@ -512,10 +546,23 @@ int rrt_render_frames(rrt_scene* s, const rrt_render_params* params, int32_t n_f
     return RRT_OK;
 }
 
+#if defined(RRT_PROBE) && RRT_PROBE
+extern "C" int rrt_debug_probe(const DevScene*, const DevParams*, int, int, int, float*, unsigned long long*);
+// experiment builds only (tools/probe.py)
+int rrt_debug_probe_scene(rrt_scene* s, const rrt_render_params* p, int kind, int mode, int reps, float* ms,
+                          unsigned long long* out) {
+    DevParams P;
+    int rc = make_params(s, p, nullptr, &P);
+    if (rc) return rc;
+    CU(cudaSetDevice(s->device));
+    return rrt_debug_probe(&s->dev, &P, kind, mode, reps, ms, out);
+}
+#endif
+
 int rrt_render_counters(rrt_scene* s, const rrt_render_params* p, uint32_t* fb, rrt_counters* out) {
     if (!s || !out) return fail(RRT_ERR_INVALID, "null argument");
     DevParams P;
-    int rc = make_params(p, nullptr, &P);
+    int rc = make_params(s, p, nullptr, &P);
     if (rc) return rc;
     CU(cudaSetDevice(s->device));
     const size_t n = (size_t)P.W * P.H;
@@ -558,7 +605,7 @@ int rrt_trace_rays(rrt_scene* s, uint64_t n, const double* o, const double* d, c
     if (max_t) CU(cudaMemcpy(bm.p, max_t, n * 8, cudaMemcpyHostToDevice));
     CU(cudaMemset(buv.p, 0, n * 24));
     CU(launch_trace(s->dev, n, (const double*)bo.p, (const double*)bd.p, max_t ? (const double*)bm.p : nullptr,
-                    (int32_t*)bt.p, (double*)buv.p, 0));
+                    (int32_t*)bt.p, (double*)buv.p, s->search_mode != 0, 0));
     CU(cudaMemcpy(out_tri, bt.p, n * 4, cudaMemcpyDeviceToHost));
     if (out_tuv) {
         // "untouched on miss": copy through a staging vector and merge
@@ -574,7 +621,7 @@ int rrt_ray_colours(rrt_scene* s, const rrt_render_params* p, uint64_t n, const 
                     uint8_t* out_rgb) {
     if (!s || (n && (!o || !d || !out_rgb))) return fail(RRT_ERR_INVALID, "null argument");
     DevParams P;
-    int rc = make_params(p, nullptr, &P);
+    int rc = make_params(s, p, nullptr, &P);
     if (rc) return rc;
     if (n == 0) return RRT_OK;
     CU(cudaSetDevice(s->device));
@@ -619,7 +666,7 @@ int rrt_octree_flatten_stats(const rrt_octree* t, const double* v, rrt_scene_sta
     if (!t || !out || (t->t.n_tris && !v)) return fail(RRT_ERR_INVALID, "null argument");
     const auto t0 = std::chrono::steady_clock::now();
     FlatScene flat;
-    flatten(t->t, v, cull_threshold(), cull_leaf(), &flat);
+    flatten(t->t, v, cull_threshold(), cull_leaf(), &flat, !(std::getenv("RRT_SEARCH_MODE") && std::atoi(std::getenv("RRT_SEARCH_MODE")) == 0));
     if (seconds) *seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     std::memset(out, 0, sizeof *out);
     out->n_tris = t->t.n_tris;

@@ -36,6 +36,8 @@ struct DevScene {
     uint32_t root_tri_count;   // nodes[0].triangle_count analogue: 0 => every ray misses (ray.rs:112-114)
     uint32_t planes_safe;      // octree planes satisfy the range/order conditions of the FMA quotient path
     double cull_o_max;         // f32 culling: rays with an |origin component| above this are not culled
+    uint32_t global_root;      // 1 + root of the scene-wide culling hierarchy (FlatScene::global_root), 0 = none
+    uint32_t sparse_ok;        // FlatScene::sparse_ok
 };
 
 struct DevCounters {

@@ -337,8 +337,7 @@ struct CullBuilder {
 
     double scale;                     // FlatScene::scale
     bool indirect = false;            // ids[] are RECORD indices and every leaf is one record (the scene-wide hierarchy)
-    uint32_t* next = nullptr;         // indirect: `out` is pre-sized and inner nodes are handed out from this counter
-                                      // (atomically: large subtrees are built as OpenMP tasks on disjoint ranges)
+    uint32_t* next = nullptr;         // indirect: non-null selects build_tasks (`out` is pre-sized, slots are positional)
 
 #if RRT_CULL_F32
     void pad_box(double* b) const {
@@ -467,7 +466,7 @@ struct CullBuilder {
     // Builds the subtree over [lo,hi) (hi-lo > leaf_max) and returns its DevCull index. SAH splits can be
     // arbitrarily unbalanced, so below depth 30 the split is by count: total depth <= 30 + 28 < kMaxCullDepth.
     uint32_t build(uint32_t lo, uint32_t hi, int depth = 0) {
-        if (next) return build_tasks(lo, hi, depth);
+        if (next) return build_tasks(lo, hi, depth, 0u);
         const uint32_t me = (uint32_t)out.size();
         out.emplace_back();
         const uint32_t mid = (tight && depth < 30) ? split(lo, hi) : lo + (hi - lo) / 2;
@@ -485,14 +484,15 @@ struct CullBuilder {
         }
         return me;
     }
-    // Same tree, `out` pre-sized (a binary tree with one record per leaf has n - 1 inner nodes): the two halves of a
-    // large range are independent (split() permutes [lo,hi) only) and are built as tasks.
-    uint32_t build_tasks(uint32_t lo, uint32_t hi, int depth) {
-        uint32_t me;
-#pragma omp atomic capture
-        me = (*next)++;
+    // Same tree, `out` pre-sized: a binary tree with one record per leaf over [lo, hi) has hi - lo - 1 inner nodes, so
+    // the subtree over [lo, hi) owns the slots [slot, slot + hi - lo - 1) — its root at `slot`, the left half right
+    // behind it, the right half behind that.  The numbering is therefore independent of scheduling, and the two halves
+    // of a large range (split() permutes [lo, hi) only) are built as independent OpenMP tasks.
+    uint32_t build_tasks(uint32_t lo, uint32_t hi, int depth, uint32_t slot) {
+        const uint32_t me = slot;
         const uint32_t mid = (tight && depth < 30) ? split(lo, hi) : lo + (hi - lo) / 2;
         const uint32_t r[3] = {lo, mid, hi};
+        const uint32_t child_slot[2] = {slot + 1u, slot + (mid - lo)};
         uint32_t child[2];
         for (int s = 0; s < 2; ++s) {
             double b[6];
@@ -504,11 +504,11 @@ struct CullBuilder {
                 child[s] = leaf_word(ids[r[s]], 1u);
             } else if (n > 50000u) {
                 uint32_t* dst = &child[s];
-                const uint32_t a = r[s], e = r[s + 1];
-#pragma omp task firstprivate(dst, a, e, depth)
-                *dst = build_tasks(a, e, depth + 1);
+                const uint32_t a = r[s], e = r[s + 1], cs = child_slot[s];
+#pragma omp task firstprivate(dst, a, e, depth, cs)
+                *dst = build_tasks(a, e, depth + 1, cs);
             } else {
-                child[s] = build_tasks(r[s], r[s + 1], depth + 1);
+                child[s] = build_tasks(r[s], r[s + 1], depth + 1, child_slot[s]);
             }
         }
 #pragma omp taskwait
@@ -520,11 +520,14 @@ struct CullBuilder {
 
 }  // namespace
 
-void flatten(const HostOctree& t, const double* v, uint32_t cull_threshold, uint32_t cull_leaf, FlatScene* out) {
+void flatten(const HostOctree& t, const double* v, uint32_t cull_threshold, uint32_t cull_leaf, FlatScene* out,
+             bool global_hierarchy) {
     out->nodes.clear();
     out->tris.clear();
     out->cull.clear();
     out->n_stored = out->root_list = out->max_list = 0;
+    out->global_root = 0;
+    out->sparse_ok = false;
     out->planes_safe = true;
     out->max_depth = t.max_depth;
     if (t.nodes.empty() || t.nodes[0].triangle_count == 0) {
@@ -692,18 +695,44 @@ void flatten(const HostOctree& t, const double* v, uint32_t cull_threshold, uint
         }
         std::vector<DevCull>().swap(pc);
     }
-    // EXPERIMENT (RRT_GLOBAL_CULL=1 at scene creation; read by -DRRT_SHADOW_FILTER=2 builds only): one culling hierarchy
-    // over ALL records of the scene, every leaf a single record, for the any-accepted-hit filter of rrt_trace.cuh — which
-    // record belongs to which octree node does not matter to that question.  Its root + 1 is parked in the padding of
-    // node 0 (0 = none); the default flatten is unchanged byte for byte.
-    const char* gc = std::getenv("RRT_GLOBAL_CULL");
-    if (gc && std::atoi(gc) != 0 && tight && out->scale < INFINITY && out->tris.size() > 1 && out->tris.size() < (1u << 28)) {
+    // The way UP from a record: its node, a node's parent and which reference child of it the node is; and whether
+    // every stored triangle lies inside the box of the node that stores it (false when a triangle pokes out of the
+    // root box, utils.rs:145 / octree.rs:71-73) with a root box of sane size — sparse_closest's precondition (a).
+    {
+        bool inside = true;
+        for (size_t d = 0; d < out->nodes.size(); ++d) {
+            DevNode& dn = out->nodes[d];
+            uint32_t rank = 0;
+            for (int k = 0; k < 8; ++k)
+                if (dn.child_mask & (1u << k)) {
+                    DevNode& ch = out->nodes[dn.first_child + rank++];
+                    ch.parent = (uint32_t)d;
+                    ch.child_slot = (uint32_t)k;
+                }
+            const double* nb = t.nodes[order[d]].box;
+            for (uint32_t r = dn.tri_first; r < dn.tri_first + dn.tri_n; ++r) {
+                out->tris[r].node = (uint32_t)d;
+                double tb[6];
+                tri_box(v + 9 * (size_t)out->tris[r].id, tb);
+                for (int k = 0; k < 3; ++k)
+                    if (!(tb[k] >= nb[k] && tb[3 + k] <= nb[3 + k])) inside = false;
+            }
+        }
+        double rmax = 0.0;
+        for (int k = 0; k < 6; ++k) rmax = std::fmax(rmax, std::fabs(t.nodes[0].box[k]));
+        out->sparse_ok = inside && rmax <= 1e4 * out->scale;
+    }
+    // ONE more culling hierarchy over ALL records of the scene, every leaf a single record, for the searches that go
+    // round the octree walk (rrt_trace.cuh: scene_clear, sparse_closest) — which record belongs to which octree node
+    // does not matter to their questions.  n - 1 inner nodes, built as OpenMP tasks on disjoint ranges.
+    if (global_hierarchy && tight && out->scale < INFINITY && out->tris.size() > 1 && out->tris.size() < (1u << 28)) {
         const size_t nr = out->tris.size();
         std::vector<uint32_t> recs(nr);
         std::vector<double> boxes(6 * nr);
-        for (size_t r = 0; r < nr; ++r) {
+#pragma omp parallel for schedule(static)
+        for (long long r = 0; r < (long long)nr; ++r) {
             recs[r] = (uint32_t)r;
-            tri_box(v + 9 * (size_t)out->tris[r].id, &boxes[6 * r]);
+            tri_box(v + 9 * (size_t)out->tris[r].id, &boxes[6 * (size_t)r]);
         }
         std::vector<DevCull> piece(nr - 1);
         uint32_t next = 0;
@@ -713,36 +742,13 @@ void flatten(const HostOctree& t, const double* v, uint32_t cull_threshold, uint
 #pragma omp single
         root = cb.build(0, (uint32_t)nr);
         const uint32_t base = (uint32_t)out->cull.size();
+        out->cull.reserve(out->cull.size() + piece.size());
         for (DevCull& c : piece) {
             for (int k = 0; k < 2; ++k)
                 if (!(c.child[k] & 0x80000000u)) c.child[k] += base;
             out->cull.push_back(c);
         }
-        out->nodes[0]._pad2[0] = root + base + 1u;
-        // for the sparse closest-hit experiment (RRT_SPARSE_PRIMARY, rrt_trace.cuh): the way UP from a record — its node
-        // in DevTri::_pad, a node's parent in DevNode::_pad and its reference child index in _pad2[1] — and, in node 0's
-        // _pad, whether every stored triangle lies inside the box of the node that stores it (false when a triangle pokes
-        // out of the root box, utils.rs:145 / octree.rs:71-73)
-        uint32_t inside = 1u;
-        for (size_t d = 0; d < out->nodes.size(); ++d) {
-            DevNode& dn = out->nodes[d];
-            uint32_t rank = 0;
-            for (int k = 0; k < 8; ++k)
-                if (dn.child_mask & (1u << k)) {
-                    DevNode& ch = out->nodes[dn.first_child + rank++];
-                    ch._pad = (uint32_t)d;
-                    ch._pad2[1] = (uint32_t)k;
-                }
-            const double* nb = t.nodes[order[d]].box;
-            for (uint32_t r = dn.tri_first; r < dn.tri_first + dn.tri_n; ++r) {
-                out->tris[r]._pad = (uint32_t)d;
-                double tb[6];
-                tri_box(v + 9 * (size_t)out->tris[r].id, tb);
-                for (int k = 0; k < 3; ++k)
-                    if (!(tb[k] >= nb[k] && tb[3 + k] <= nb[3 + k])) inside = 0u;
-            }
-        }
-        out->nodes[0]._pad = inside;
+        out->global_root = root + base + 1u;
     }
 }
 

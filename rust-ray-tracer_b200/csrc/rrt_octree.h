@@ -54,10 +54,11 @@ struct alignas(128) DevNode {
                                  // (octree.rs:136-210) — 9 distinct slab numerators instead of 48
     uint32_t cull_root;          // entry of this list's culling hierarchy: a DevCull index, or a leaf word
                                  // (bit31 | (count-1) << 28 | first record) when the list is short
-    uint32_t _pad;
+    uint32_t parent;             // device index of the parent node (root: 0) ...
     float list_box[6];           // conservative (padded, outward-rounded) f32 box of the node's OWN list:
                                  // a ray that misses it cannot be accepted by any record of the list
-    uint32_t _pad2[2];
+    uint32_t child_slot;         // ... and which reference child (0..7, octree.rs:216-225) of it this node is
+    uint32_t _pad;
 };
 static_assert(sizeof(DevNode) == 128, "DevNode layout");
 
@@ -66,7 +67,7 @@ static_assert(sizeof(DevNode) == 128, "DevNode layout");
 struct alignas(16) DevTri {
     double v1[3], e1[3], e2[3];
     uint32_t id;   // index in `f`-line order (what hit-id planes report; also the in-list tie order)
-    uint32_t _pad;
+    uint32_t node; // device index of the octree node whose list holds this record
 };
 static_assert(sizeof(DevTri) == 80, "DevTri layout");
 
@@ -126,6 +127,9 @@ struct FlatScene {
     bool planes_safe = true;   // every octree plane is 0 or has magnitude in [2^-400, 2^401), and the three planes
                                // of every axis are ordered min <= mid <= max (rrt_trace.cuh)
     double scale = 1.0;        // S = max(1, largest |coordinate| of a stored triangle): culling pad / eligibility unit
+    uint32_t global_root = 0;  // 1 + DevCull index of the root of the scene-wide hierarchy over ALL records (0 = none)
+    bool sparse_ok = false;    // every stored triangle lies inside its node's box and the root box is at most 1e4 S
+                               // across: precondition (a) of sparse_closest (rrt_trace.cuh)
 };
 
 // Flatten: renumber kept nodes breadth-first (siblings consecutive), concatenate node lists.
@@ -133,6 +137,9 @@ struct FlatScene {
 // leaves hold at most cull_leaf (1..8) records; shorter lists are one leaf (every record is tested).
 // 0 = culling off: long lists still go through the same hierarchy code, but with infinite boxes, so
 // every record of the list is tested (the exact linear scan of the reference, in another order).
-void flatten(const HostOctree& t, const double* v, uint32_t cull_threshold, uint32_t cull_leaf, FlatScene* out);
+// global_hierarchy: also build the scene-wide hierarchy (one more DevCull per record) for the searches that go round
+// the octree walk (rrt_trace.cuh: scene_clear, sparse_closest).
+void flatten(const HostOctree& t, const double* v, uint32_t cull_threshold, uint32_t cull_leaf, FlatScene* out,
+             bool global_hierarchy = true);
 
 }  // namespace rrt

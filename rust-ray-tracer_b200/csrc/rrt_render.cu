@@ -30,27 +30,25 @@ __device__ unsigned long long g_tl[4 + 256];   // [0] min start, [1] min queue-d
 __device__ __forceinline__ unsigned long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
 #endif
 
-#if RRT_SHADOW_FILTER
-// Experiment builds only (rrt_trace.cuh, RRT_SHADOW_FILTER): frame-to-frame switch of the shadow filter.  The filter pays
-// where shadow queries mostly come back None (c4: 99 %) and costs where they are mostly occluded (c5: none come back
-// None), so every launch counts what the queries that went through the filter returned, a one-thread kernel behind it
-// sets the switch for the next launch, and 1/16 of the pixel groups keep probing while it is off.  Results do not
-// depend on the switch (both paths are exact).  DevParams::shadow_filter: 0 off, 1 this switch, 2 always on.
-// The sparse closest-hit search of camera rays (RRT_SPARSE_PRIMARY) is switched the same way by how many of them it
-// answered itself: a camera inside the geometry (c5) has every ray handed over by the `tmin > 0` rule.
-__device__ unsigned int g_fstat[8] = {0u, 0u, 1u, 0u, 0u, 0u, 1u, 0u};   // None, Some, filter on, launches | answered, handed over, sparse on
-__global__ void filter_update_kernel() {
-    const unsigned int none = g_fstat[0], some = g_fstat[1];
-    if (none + some >= 64u) g_fstat[2] = (2u * none >= none + some) ? 1u : 0u;
-    const unsigned int ans = g_fstat[4], handed = g_fstat[5];
-    if (ans + handed >= 64u) g_fstat[6] = (2u * ans >= ans + handed) ? 1u : 0u;
-    g_fstat[0] = 0u;
-    g_fstat[1] = 0u;
-    g_fstat[4] = 0u;
-    g_fstat[5] = 0u;
-    g_fstat[3] += 1u;
+// Frame-to-frame switch of the two searches that go round the octree walk (rrt_trace.cuh).  Each pays where it answers
+// most of the rays it is tried on (c4: 98 % of the shadow queries, all camera rays; c2: 77 % / 99.9 %) and costs where
+// it does not (c5: every shadow ray is occluded and the camera sits inside the soup — a handed-over ray pays the search
+// AND the walk).  So every launch counts what the searches returned (DevParams::fstat, per scene handle) and a
+// one-thread kernel behind it sets the switches for the next launch: a search stays on while it answers at least half
+// of its rays (measured break-even, profiles/r02_experiments.md), and every kProbeEvery-th frame runs with both on
+// again, which is how a switched-off search gets back in when the camera has moved.  Results do not depend on the
+// switches: both paths are exact.
+constexpr uint32_t kProbeEvery = 32u;
+__global__ void search_switch_kernel(uint32_t* __restrict__ fs) {
+    const uint32_t a = fs[0], h = fs[1];
+    if (a + h >= 64u) fs[2] = (2ull * a >= (unsigned long long)a + h) ? 1u : 0u;
+    const uint32_t sa = fs[4], sh = fs[5];
+    if (sa + sh >= 64u) fs[6] = (2ull * sa >= (unsigned long long)sa + sh) ? 1u : 0u;
+    fs[8] = a; fs[9] = h; fs[10] = sa; fs[11] = sh;   // what the decision was made from (rrt_scene_search_state)
+    fs[0] = fs[1] = fs[4] = fs[5] = 0u;
+    const uint32_t frames = ++fs[3];
+    if (frames % kProbeEvery == 0u) { fs[2] = 1u; fs[6] = 1u; }
 }
-#endif
 
 // Persistent render kernel (Scene::draw_scene, engine.rs:186-255).  One lane = one supersample at a time.
 // Whenever lanes of a warp run dry — their ray missed, or finished its shadow / mirror chain early — they
@@ -68,9 +66,7 @@ render_kernel(const DevScene sc, const __grid_constant__ DevParams P, uint32_t* 
               const uint32_t* __restrict__ order, uint32_t* __restrict__ cost) {
     const unsigned lane = threadIdx.x & 31u;
     const unsigned lt_mask = (1u << lane) - 1u;
-    __shared__ double park_s[RRT_PARK ? kParkWords * kBlock : 1];
-    double* const park = park_s + (RRT_PARK ? threadIdx.x : 0);
-    RayStateT<kBlock> st;
+    RayState st;
     bool active = false, drained = false;
     size_t pix = 0, out = 0;   // compact pixel index (accumulator, hit ids) / index the finished pixel is stored at
     unsigned k = 0;
@@ -81,12 +77,13 @@ render_kernel(const DevScene sc, const __grid_constant__ DevParams P, uint32_t* 
     __shared__ uint2 tile_info_s[HINT ? kBlock / 32 : 1];
     uint2& tile_info = tile_info_s[HINT ? threadIdx.x >> 5 : 0];
     if (HINT && lane == 0) tile_info = make_uint2(0xFFFFFFFFu, 0u);
-#if RRT_SHADOW_FILTER
-    __shared__ unsigned int fstat_s[kBlock / 32][4];   // this warp's filtered shadow queries: came back None / Some;
-    unsigned int* const fstat_w = fstat_s[threadIdx.x >> 5];   // its sparse camera rays: answered / handed over
-    bool prev_miss = false;   // RRT_PRIMARY_FILTER: this lane's previous sample hit nothing
+    // what this warp's searches returned: shadow queries answered / handed to the walk, camera rays likewise
+    __shared__ unsigned int fstat_s[kBlock / 32][4];
+    unsigned int* const fstat_w = fstat_s[threadIdx.x >> 5];
     if (lane < 4) fstat_w[lane] = 0u;
-#endif
+    const bool switched = P.search_mode == 1 || P.search_mode == 3;
+    const bool filter_on = P.search_mode == 2 || (switched && P.fstat[2] != 0u);
+    const bool sparse_on = (P.search_mode == 2 || (switched && P.fstat[6] != 0u)) && sc.sparse_ok != 0u;
     __syncwarp();
 #if RRT_TIMELINE
     if (lane == 0) atomicMin(&g_tl[0], gtime());
@@ -144,25 +141,24 @@ render_kernel(const DevScene sc, const __grid_constant__ DevParams P, uint32_t* 
         // ---- one traversal for every lane that carries a ray, whatever its kind
         if (active) {
             Hit h;
-#if RRT_SHADOW_FILTER
             const bool was_shadow = st.shadow;
-            bool use_filter = P.shadow_filter != 0;
-            if (was_shadow) use_filter = use_filter && (P.shadow_filter == 2 || g_fstat[2] != 0u || ((pix >> 6) & 15u) == 0u);
-            else if (RRT_SPARSE_PRIMARY) use_filter = use_filter && st.depth == 0 &&
-                                                      (P.shadow_filter == 2 || g_fstat[6] != 0u || ((pix >> 6) & 15u) == 0u);
-            else use_filter = use_filter && st.depth == 0 && RRT_PRIMARY_FILTER && prev_miss;
-            uint32_t sparse_outcome = 0u;
-            traverse<COUNT>(sc, st.so, st.sd, st.smax, was_shadow, h, tc_total, use_filter, &sparse_outcome);
-            if (use_filter && was_shadow) atomicAdd(fstat_w + (h.id == kNone ? 0 : 1), 1u);
-            if (sparse_outcome != 0u) atomicAdd(fstat_w + 1 + sparse_outcome, 1u);
-#else
-            traverse<COUNT>(sc, st.so, st.sd, st.smax, st.shadow, h, tc_total);
-#endif
-            if (st.advance<COUNT>(sc, P, h, park)) {
+            const uint32_t allow = was_shadow ? (filter_on ? kTryFilter : 0u) : ((sparse_on && st.depth == 0) ? kTrySparse : 0u);
+            uint32_t outcome;
+            traverse<COUNT>(sc, st.so, st.sd, st.smax, was_shadow, h, tc_total, allow, &outcome);
+            if (P.search_mode == 1) {   // per warp: how many of its searches answered / handed over (lanes here are a subset)
+                const unsigned here = __activemask();
+                const unsigned tried = __ballot_sync(here, outcome != 0u), ans = __ballot_sync(here, outcome == 1u),
+                               shad = __ballot_sync(here, was_shadow);
+                if (tried != 0u && (int)lane == __ffs(here) - 1) {
+                    fstat_w[0] += __popc(ans & shad);
+                    fstat_w[1] += __popc(tried & ~ans & shad);
+                    fstat_w[2] += __popc(ans & ~shad);
+                    fstat_w[3] += __popc(tried & ~ans & ~shad);
+                }
+                __syncwarp(here);
+            }
+            if (st.advance<COUNT>(sc, P, h)) {
                 active = false;
-#if RRT_SHADOW_FILTER
-                prev_miss = st.hit0 < 0;
-#endif
                 if (hit_ids) hit_ids[pix * 4 + k] = st.hit0;
                 const uint32_t add = sample_add(st.res);
                 const uint32_t old = atomicAdd(acc + pix, add);
@@ -170,10 +166,8 @@ render_kernel(const DevScene sc, const __grid_constant__ DevParams P, uint32_t* 
             }
         }
     }
-#if RRT_SHADOW_FILTER
     __syncwarp();
-    if (lane < 4 && fstat_w[lane] != 0u) atomicAdd(&g_fstat[lane < 2 ? lane : lane + 2], fstat_w[lane]);
-#endif
+    if (P.search_mode == 1 && lane < 4 && fstat_w[lane] != 0u) atomicAdd(P.fstat + (lane < 2 ? lane : lane + 2), fstat_w[lane]);
 #if RRT_TIMELINE
     if (lane == 0) {
         const unsigned long long t = gtime();
@@ -198,13 +192,13 @@ render_kernel(const DevScene sc, const __grid_constant__ DevParams P, uint32_t* 
 // Ray::intersect_with_octant_with_max_t for arbitrary rays (ray.rs:104-168)
 __global__ void __launch_bounds__(kBlock)
 trace_kernel(const DevScene sc, const uint64_t n, const double* __restrict__ o, const double* __restrict__ d,
-             const double* __restrict__ max_t, int32_t* __restrict__ out_tri, double* __restrict__ out_tuv) {
+             const double* __restrict__ max_t, int32_t* __restrict__ out_tri, double* __restrict__ out_tuv, const uint32_t allow) {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     Hit h;
     TraceCount tc;
     const double mt = max_t ? max_t[i] : __longlong_as_double(0x7FF0000000000000ll);
-    traverse<false>(sc, V3{o[3 * i], o[3 * i + 1], o[3 * i + 2]}, V3{d[3 * i], d[3 * i + 1], d[3 * i + 2]}, mt, false, h, tc);
+    traverse<false>(sc, V3{o[3 * i], o[3 * i + 1], o[3 * i + 2]}, V3{d[3 * i], d[3 * i + 1], d[3 * i + 2]}, mt, false, h, tc, allow);
     out_tri[i] = (h.id == kNone) ? -1 : (int32_t)h.id;
     if (h.id != kNone && out_tuv) {
         double u, v;
@@ -215,19 +209,20 @@ trace_kernel(const DevScene sc, const uint64_t n, const double* __restrict__ o, 
 
 // RayTracer::get_ray_colour for arbitrary rays (raytracer.rs:29-31)
 __global__ void __launch_bounds__(kBlock)
-colour_kernel(const DevScene sc, const __grid_constant__ DevParams P, const uint64_t n, const double* __restrict__ o,
-              const double* __restrict__ d, uint8_t* __restrict__ out_rgb) {
+colour_kernel(const DevScene sc, const __grid_constant__ DevParams P, const uint64_t n,
+              const double* __restrict__ o, const double* __restrict__ d, uint8_t* __restrict__ out_rgb) {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    __shared__ double park_s[RRT_PARK ? kParkWords * kBlock : 1];
-    double* const park = park_s + (RRT_PARK ? threadIdx.x : 0);
     if (i >= n) return;
-    RayStateT<kBlock> st;
+    RayState st;
+    // every search on every ray it applies to (also mirror rays: their origins lie INSIDE the geometry, which the
+    // render kernel leaves to the walk — here they test the hand-over rules) unless the caller asked for the walk only
+    const uint32_t allow = P.search_mode != 0 ? (kTryFilter | kTrySparse) : 0u;
     TraceCount tc;
     st.begin(V3{o[3 * i], o[3 * i + 1], o[3 * i + 2]}, V3{d[3 * i], d[3 * i + 1], d[3 * i + 2]});
     Hit h;
     do {
-        traverse<false>(sc, st.so, st.sd, st.smax, st.shadow, h, tc);
-    } while (!st.advance<false>(sc, P, h, park));
+        traverse<false>(sc, st.so, st.sd, st.smax, st.shadow, h, tc, allow);
+    } while (!st.advance<false>(sc, P, h));
     const uint32_t c = st.res;
     out_rgb[3 * i] = (uint8_t)(c & 255u); out_rgb[3 * i + 1] = (uint8_t)((c >> 8) & 255u); out_rgb[3 * i + 2] = (uint8_t)((c >> 16) & 255u);
 }
@@ -293,6 +288,89 @@ __global__ void iota_kernel(uint32_t* __restrict__ v, uint32_t n) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) v[i] = i;
 }
+
+#ifndef RRT_PROBE
+#define RRT_PROBE 0
+#endif
+#if RRT_PROBE
+// ---------------------------------------------------------------- experiment builds only (-DRRT_PROBE=1)
+// What would each kind of traversal cost as a kernel of its own (own register budget, every lane on the same kind of
+// ray)?  probe_fill writes one ray per sample — kind 0: the camera ray, kind 1: the ray the shading state machine asks
+// for next after the camera ray's hit (light 1's shadow query, or the mirror ray) — and probe_trace runs ONE traversal
+// flavour over the buffer.  Not product code: tools/probe.py drives it, profiles/r02_experiments.md has the numbers.
+struct ProbeRay { double ox, oy, oz, dx, dy, dz, max_t; uint32_t kind, _pad; };   // kind: 0 none, 1 closest hit, 2 any hit
+
+__global__ void __launch_bounds__(kBlock)
+probe_fill_kernel(const DevScene sc, const __grid_constant__ DevParams P, ProbeRay* __restrict__ rays, const int tiles_x,
+                  const unsigned long long total, const int kind) {
+    const unsigned long long s = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= total) return;
+    ProbeRay r{};
+    const unsigned long long tile = s >> 5;
+    int col, krow;
+    unsigned k;
+    sample_pixel(tile >> 3, (unsigned)tile & 7u, (unsigned)s & 31u, tiles_x, col, krow, k);
+    V3 d;
+    if (col < P.W && krow < P.n_rows_local && primary_ray(P, col, buffer_row(P, krow), k, d)) {
+        if (kind == 0) {
+            r = ProbeRay{P.ox, P.oy, P.oz, d.x, d.y, d.z, __longlong_as_double(0x7FF0000000000000ll), 1u, 0u};
+        } else {
+            RayState st;
+            st.begin(V3{P.ox, P.oy, P.oz}, d);
+            Hit h;
+            TraceCount tc;
+            traverse<false>(sc, st.so, st.sd, st.smax, false, h, tc, 0u);
+            if (!st.advance<false>(sc, P, h))
+                r = ProbeRay{st.so.x, st.so.y, st.so.z, st.sd.x, st.sd.y, st.sd.z, st.smax, st.shadow ? 2u : 1u, 0u};
+        }
+    }
+    rays[s] = r;
+}
+
+#ifndef RRT_PROBE_MIN_BLOCKS
+#define RRT_PROBE_MIN_BLOCKS 1
+#endif
+// mode 0: the exact octree walk; mode 1: only the search that goes round it (sparse_closest for closest-hit rays,
+// shadow_clear for any-hit rays) — rays it cannot answer are COUNTED, not walked
+template <int MODE>
+__global__ void __launch_bounds__(kBlock, RRT_PROBE_MIN_BLOCKS)
+probe_trace_kernel(const DevScene sc, const ProbeRay* __restrict__ rays, const unsigned long long total,
+                   unsigned long long* __restrict__ out) {
+    const unsigned long long s = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned long long n_rays = 0, n_answered = 0, sum = 0;
+    if (s < total) {
+        const ProbeRay r = rays[s];
+        if (r.kind != 0u) {
+            n_rays = 1;
+            const V3 o{r.ox, r.oy, r.oz}, d{r.dx, r.dy, r.dz};
+            Hit h;
+            h.id = kNone; h.rec = 0; h.t = r.max_t;
+            TraceCount tc;
+            if (MODE == 0) {
+                traverse<false>(sc, o, d, r.max_t, r.kind == 2u, h, tc, 0u);
+                n_answered = 1;
+            } else if (r.kind == 2u) {
+                n_answered = scene_clear<false>(search_scene(sc), o, d, r.max_t, tc) ? 1 : 0;
+            } else {
+                const SparseResult sr = sparse_closest<false>(search_scene(sc), o, d, tc);
+                n_answered = sr.status;
+                h.id = sr.id;
+            }
+            sum = h.id;
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        n_rays += __shfl_xor_sync(0xFFFFFFFFu, n_rays, o);
+        n_answered += __shfl_xor_sync(0xFFFFFFFFu, n_answered, o);
+        sum += __shfl_xor_sync(0xFFFFFFFFu, sum, o);
+    }
+    if ((threadIdx.x & 31u) == 0u) {
+        if (n_rays) atomicAdd(out, n_rays);
+        if (n_answered) atomicAdd(out + 1, n_answered);
+        if (sum) atomicAdd(out + 2, sum);
+    }
+}
+#endif
 
 }  // namespace
 
@@ -406,9 +484,7 @@ cudaError_t launch_render(const DevScene& sc, const DevParams& P, uint32_t* d_fb
     else
         render_kernel<false, false><<<grid, kBlock, 0, stream>>>(sc, P, d_fb, d_hit, d_scratch, next, nullptr, tiles_x, total, nullptr, nullptr);
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
-#if RRT_SHADOW_FILTER
-    if (!d_counters && P.shadow_filter == 1) filter_update_kernel<<<1, 1, 0, stream>>>();
-#endif
+    if (!d_counters && P.search_mode == 1) search_switch_kernel<<<1, 1, 0, stream>>>(P.fstat);
     if (hint) {
         // next frame's order: stable sort of the blocks by this frame's cost class, on the side stream, so that it
         // overlaps whatever the caller does with the frame next (copy to the host, gather, L2 flush of a benchmark)
@@ -440,12 +516,51 @@ extern "C" int rrt_debug_timeline(unsigned long long* out, int reset) {
 }
 #endif
 
+#if RRT_PROBE
+// experiment builds only: out[0..2] = rays, answered, checksum; ms[0] = fill, ms[1] = trace (CUDA events)
+extern "C" int rrt_debug_probe(const DevScene* scp, const DevParams* Pp, int kind, int mode, int reps, float* ms,
+                               unsigned long long* out) {
+    const DevScene& sc = *scp;
+    const DevParams& P = *Pp;
+    const int tiles_x = (P.W + kTileW - 1) / kTileW, tiles_y = (P.n_rows_local + kTileH - 1) / kTileH;
+    const unsigned long long total = (unsigned long long)tiles_x * tiles_y * (kTileW * kTileH * 4);
+    ProbeRay* rays = nullptr;
+    unsigned long long* d_out = nullptr;
+    if (cudaMalloc(&rays, total * sizeof(ProbeRay)) != cudaSuccess || cudaMalloc(&d_out, 24) != cudaSuccess) return 1;
+    cudaEvent_t e0, e1, e2;
+    cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventCreate(&e2);
+    const unsigned grid = (unsigned)((total + kBlock - 1) / kBlock);
+    cudaEventRecord(e0);
+    probe_fill_kernel<<<grid, kBlock>>>(sc, P, rays, tiles_x, total, kind);
+    cudaEventRecord(e1);
+    float best = 1e30f;
+    for (int i = 0; i < reps; ++i) {
+        cudaMemset(d_out, 0, 24);
+        cudaEventRecord(e1);
+        if (mode == 0) probe_trace_kernel<0><<<grid, kBlock>>>(sc, rays, total, d_out);
+        else probe_trace_kernel<1><<<grid, kBlock>>>(sc, rays, total, d_out);
+        cudaEventRecord(e2);
+        if (cudaEventSynchronize(e2) != cudaSuccess) return 2;
+        float t = 0;
+        cudaEventElapsedTime(&t, e1, e2);
+        best = t < best ? t : best;
+    }
+    cudaEventElapsedTime(&ms[0], e0, e1);
+    ms[1] = best;
+    cudaMemcpy(out, d_out, 24, cudaMemcpyDeviceToHost);
+    cudaFree(rays); cudaFree(d_out);
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2);
+    return cudaGetLastError() == cudaSuccess ? 0 : 3;
+}
+#endif
+
 size_t render_scratch_words(int n_rows_local, int W) { return (((size_t)n_rows_local * W + 1) & ~(size_t)1) + 2; }
 
 cudaError_t launch_trace(const DevScene& sc, uint64_t n, const double* o, const double* d, const double* max_t,
-                         int32_t* out_tri, double* out_tuv, cudaStream_t stream) {
+                         int32_t* out_tri, double* out_tuv, bool searches, cudaStream_t stream) {
     if (n == 0) return cudaSuccess;
-    trace_kernel<<<(unsigned)((n + kBlock - 1) / kBlock), kBlock, 0, stream>>>(sc, n, o, d, max_t, out_tri, out_tuv);
+    trace_kernel<<<(unsigned)((n + kBlock - 1) / kBlock), kBlock, 0, stream>>>(sc, n, o, d, max_t, out_tri, out_tuv,
+                                                                                searches ? (kTryFilter | kTrySparse) : 0u);
     return cudaGetLastError();
 }
 

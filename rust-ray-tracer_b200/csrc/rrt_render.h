@@ -35,8 +35,9 @@ struct RenderSchedule {
 cudaError_t launch_render(const DevScene& sc, const DevParams& P, uint32_t* d_fb, int32_t* d_hit, uint32_t* d_scratch,
                           DevCounters* d_counters, cudaStream_t stream, RenderSchedule* sch = nullptr);
 size_t render_scratch_words(int n_rows_local, int W);
+// searches: let rays be answered by the scene-wide hierarchy where that is exact (rrt_trace.cuh); false = walk only
 cudaError_t launch_trace(const DevScene& sc, uint64_t n, const double* o, const double* d, const double* max_t,
-                         int32_t* out_tri, double* out_tuv, cudaStream_t stream);
+                         int32_t* out_tri, double* out_tuv, bool searches, cudaStream_t stream);
 cudaError_t launch_colours(const DevScene& sc, const DevParams& P, uint64_t n, const double* o, const double* d,
                            uint8_t* out_rgb, cudaStream_t stream);
 cudaError_t launch_deinterleave(const uint32_t* g, int rows_per_block, int W, int H, int T, int G, uint32_t* fb,

@@ -17,7 +17,11 @@ struct DevParams {
     double rot[9];
     int32_t tile_rows, n_shards, shard_index, n_rows_local;  // row sharding (rrt_shard)
     int32_t full_frame;     // 1: fb is a FULL frame (possibly peer memory), owned row k goes to its buffer row
-    int32_t shadow_filter;  // read by -DRRT_SHADOW_FILTER=1 builds only: 0 off, 1 switched per launch (rrt_render.cu), 2 always on
+    int32_t search_mode;    // searches that go round the octree walk (rrt_trace.cuh): 0 never, 2 always, 1 switched per
+                            // scene handle from one launch to the next by how many rays they answered (fstat),
+                            // 3 the switches in fstat as the host set them (rrt_scene_search_mode)
+    uint32_t* fstat;        // per scene handle, device: [0] shadow queries answered, [1] handed to the walk, [2] filter on,
+                            // [3] launches, [4] camera rays answered, [5] handed over, [6] sparse search on, [7] unused
 };
 
 struct RayCount {
@@ -50,29 +54,21 @@ __device__ __forceinline__ void add_light(V3& I, const DevMaterial* __restrict__
     if (!spec) I = I + V3{0.0, 0.0, 0.0};
 }
 
-#ifndef RRT_PARK
-#define RRT_PARK 0
-#endif
-constexpr int kParkWords = 12;   // pt, n, I, view direction: the shading state that must survive a shadow traversal
-
 // Per-ray state of RayTracer::get_ray_colour_recursive (raytracer.rs:33-112) between traversals.
-// Usage:  st.begin(o, d);  do { traverse(st.so, st.sd, st.smax, st.shadow, h); } while (!st.advance(sc, P, h, park));
+// Usage:  st.begin(o, d);  do { traverse(st.so, st.sd, st.smax, st.shadow, h); } while (!st.advance(sc, P, h));
 // then st.res is the colour packed r | g<<8 | b<<16 and st.hit0 the depth-0 triangle id (-1 = miss).
 //
 // Register budget: the traversal is the hot loop and the kernel is register-bound (64 per thread), so the
-// only doubles this struct keeps in registers across a traversal are the ray handed to traverse().  The
+// only doubles this struct needs in registers across a traversal are the ray handed to traverse().  The
 // shading state a shadow query interrupts (hit point, normal, accumulated light, view direction: 12
-// doubles) is PARKED in shared memory (`park`, one column per thread, stride kParkStride doubles) while
-// the shadow ray is traced, instead of letting the compiler spill whatever it picks to local memory.
-template <int kParkStride>
-struct RayStateT {
+// doubles) is stored explicitly in `parked` while the shadow ray is traced (shared memory for it was measured
+// slower: it takes L1 capacity away from the tree data, profiles/r01_experiments.md).
+struct RayState {
     // reflection stack: local colour and reflectivity of every open level (raytracer.rs:89-101)
     double lx[kMaxReflectDepth], ly[kMaxReflectDepth], lz[kMaxReflectDepth], lk[kMaxReflectDepth];
     V3 so, sd;            // the ray to hand to traverse(); for primary / reflection rays it IS the current ray
     double smax;
-#if !RRT_PARK
-    double parked[kParkWords];
-#endif
+    double parked[12];    // pt, n, I, view direction
     uint32_t texel, res;
     int32_t hit0, mid;    // depth-0 triangle id; material of the point being shaded
     int depth, li;
@@ -101,32 +97,22 @@ struct RayStateT {
         }
     }
 
-    __device__ __forceinline__ void park_store(double* park, const V3& pt, const V3& n, const V3& I, const V3& rd) {
-#if RRT_PARK
-#define RRT_PK(i) park[(i) * kParkStride]
-#else
-#define RRT_PK(i) parked[i]
-        (void)park;
-#endif
-        RRT_PK(0) = pt.x; RRT_PK(1) = pt.y; RRT_PK(2) = pt.z;
-        RRT_PK(3) = n.x;  RRT_PK(4) = n.y;  RRT_PK(5) = n.z;
-        RRT_PK(6) = I.x;  RRT_PK(7) = I.y;  RRT_PK(8) = I.z;
-        RRT_PK(9) = rd.x; RRT_PK(10) = rd.y; RRT_PK(11) = rd.z;
+    __device__ __forceinline__ void park_store(const V3& pt, const V3& n, const V3& I, const V3& rd) {
+        parked[0] = pt.x; parked[1] = pt.y; parked[2] = pt.z;
+        parked[3] = n.x;  parked[4] = n.y;  parked[5] = n.z;
+        parked[6] = I.x;  parked[7] = I.y;  parked[8] = I.z;
+        parked[9] = rd.x; parked[10] = rd.y; parked[11] = rd.z;
     }
-    __device__ __forceinline__ void park_load(const double* park, V3& pt, V3& n, V3& I, V3& rd) const {
-#if !RRT_PARK
-        (void)park;
-#endif
-        pt = V3{RRT_PK(0), RRT_PK(1), RRT_PK(2)};
-        n = V3{RRT_PK(3), RRT_PK(4), RRT_PK(5)};
-        I = V3{RRT_PK(6), RRT_PK(7), RRT_PK(8)};
-        rd = V3{RRT_PK(9), RRT_PK(10), RRT_PK(11)};
-#undef RRT_PK
+    __device__ __forceinline__ void park_load(V3& pt, V3& n, V3& I, V3& rd) const {
+        pt = V3{parked[0], parked[1], parked[2]};
+        n = V3{parked[3], parked[4], parked[5]};
+        I = V3{parked[6], parked[7], parked[8]};
+        rd = V3{parked[9], parked[10], parked[11]};
     }
 
     // Consumes the result of the traversal just made; returns true when the colour is final.
     template <bool COUNT>
-    __device__ __forceinline__ bool advance(const DevScene& sc, const DevParams& P, const Hit& h, double* park) {
+    __device__ __forceinline__ bool advance(const DevScene& sc, const DevParams& P, const Hit& h) {
         V3 pt, n, I, rd;
         const DevMaterial* __restrict__ mat;
         if (!shadow) {
@@ -177,7 +163,7 @@ struct RayStateT {
         } else {
             // result of the shadow query for point light `li` (raytracer.rs:232-252)
             shadow = false;
-            park_load(park, pt, n, I, rd);
+            park_load(pt, n, I, rd);
             mat = sc.materials + mid;
             if (h.id != kNone) {
                 li = P.n_lights;  // `break`: ends the WHOLE light loop (raytracer.rs:235-237)
@@ -201,7 +187,7 @@ struct RayStateT {
                 li++;
             } else {
                 // triangle_exists_between_points (raytracer.rs:164-188)
-                park_store(park, pt, n, I, rd);
+                park_store(pt, n, I, rd);
                 sd = V3{L.vec[0], L.vec[1], L.vec[2]} - pt;  // raytracer.rs:170
                 so = pt + n * P.offset;                     // raytracer.rs:172
                 smax = length(sd);                          // raytracer.rs:179

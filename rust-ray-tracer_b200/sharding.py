@@ -71,6 +71,97 @@ class HostFrame:
         abi.check(abi.lib().rrt_host_frame_barrier(self._h, float(timeout)))
 
     def close(self):
+        if self._h:
+            self.pixels = None
+            abi.lib().rrt_host_frame_close(self._h)
+            self._h = None
+
+
+class ShardedRenderer:
+    """Per-rank renderer: owns a replicated device scene and renders its interleaved tile rows.
+
+    assemble="nccl": compact rows, one all-gather + de-interleave, the full frame on EVERY rank's device.
+    assemble="peer": fused render + gather — rank 0 owns the frame(s) (rrt_frame_alloc), the other ranks map them
+        through CUDA IPC and their render kernels store finished pixels straight into rank 0's memory over NVLink;
+        the only collective left is a 4-byte all-reduce, enqueued on the render stream, that orders "all kernels
+        of this frame done".  TWO frames are used alternately (frame k lands in buffer k & 1): the token of frame
+        k+1 can only complete after rank 0 enqueued it, i.e. after whatever rank 0 put on the stream to consume
+        frame k, so by the time any rank stores frame k+2 into the buffer of frame k that consumer has run.
+        Rule for the caller: consume `frame` on the render stream (or make that stream wait for the consumer)
+        before calling render() again.
+    assemble="host": the frame is wanted in HOST memory (the reference's Canvas.buffer, engine.rs:123-128): every
+        rank renders compactly and copies ITS rows over its own PCIe link into one page-locked shared-memory
+        frame (HostFrame); assemble() = stream sync + a process-shared barrier ("frame complete"), the next
+        render() begins with a second barrier ("rank 0 is done reading").  No device-side exchange at all.
+    """
+
+    def __init__(self, ray_tracer, width, height, rank, world, tile_rows=DEFAULT_TILE_ROWS, group=None,
+                 assemble="nccl"):
+        import torch
+        self.rt, self.W, self.H = ray_tracer, width, height
+        self.rank, self.world, self.T = rank, world, tile_rows
+        self.group = group
+        self.mode = assemble if (world > 1 or assemble == "host") else "nccl"
+        self.shard = abi.Shard(tile_rows, world, rank)
+        self.n_local = int(abi.lib().rrt_shard_rows(height, C.byref(self.shard)))
+        self.rpb = rows_per_block(height, tile_rows, world)
+        dev = torch.device("cuda", ray_tracer.device)
+        self.device = dev
+        self._own_frames, self._peer_frames, self._host = [], [], None
+        self._k = 0                 # frames rendered so far (peer: selects the buffer)
+        self._outstanding = False   # host: a completed frame has not been released yet
+        if self.mode == "peer":
+            self._setup_peer_frames()
+            return
+        if self.mode == "host":
+            self._setup_host_frame()
+            return
+        self.local = torch.zeros((self.rpb, width), dtype=torch.int32, device=dev)     # u32 payload
+        self.gathered = torch.zeros((world, self.rpb, width), dtype=torch.int32, device=dev) if world > 1 else None
+        self.frame = torch.zeros((height, width), dtype=torch.int32, device=dev)
+
+    def _setup_host_frame(self):
+        import os
+        import torch.distributed as dist
+        box = [f"/rrt_frame_{os.getpid()}_{id(self) & 0xFFFFFF:x}" if self.rank == 0 else None]
+        if self.rank == 0:
+            self._host = HostFrame(box[0], self.W, self.H, self.world, create=True, device=self.rt.device)
+        if self.world > 1:
+            dist.broadcast_object_list(box, src=0, group=self.group)
+        if self.rank != 0:
+            self._host = HostFrame(box[0], self.W, self.H, self.world, create=False, device=self.rt.device)
+        self.frame = self._host.pixels        # numpy (H, W) u32 view of the shared canvas
+
+    def _setup_peer_frames(self):
+        import torch
+        import torch.distributed as dist
+        L = abi.lib()
+        handles = []
+        if self.rank == 0:
+            for _ in range(2):
+                p = C.c_void_p()
+                abi.check(L.rrt_frame_alloc(self.rt.device, self.W, self.H, C.byref(p)))
+                self._own_frames.append(p.value)
+                handle = (C.c_ubyte * 64)()
+                abi.check(L.rrt_ipc_get_handle(self.rt.device, p, handle))
+                handles.append(bytes(handle))
+        box = [handles]
+        dist.broadcast_object_list(box, src=0, group=self.group)
+        if self.rank == 0:
+            self._dest = list(self._own_frames)
+            self._frames = [torch.as_tensor(_DevFrame(d, self.H, self.W), device=self.device) for d in self._dest]
+        else:
+            for hb in box[0]:
+                q = C.c_void_p()
+                buf = (C.c_ubyte * 64).from_buffer_copy(hb)
+                abi.check(L.rrt_ipc_open_handle(self.rt.device, buf, C.byref(q)))
+                self._peer_frames.append(q.value)
+            self._dest = list(self._peer_frames)
+            self._frames = [None, None]
+        self.frame = self._frames[0]
+        self._token = torch.zeros(1, dtype=torch.int32, device=self.device)
+
+    def close(self):
         L = abi.lib()
         for q in self._peer_frames:
             L.rrt_ipc_close_handle(self.rt.device, C.c_void_p(q))

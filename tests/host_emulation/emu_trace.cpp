@@ -78,7 +78,12 @@ static rrt::DevParams emu_params(const rrt_render_params* rp, int tile_rows, int
     return P;
 }
 
+// what traverse() may try before the walk (rrt_trace.cuh: kTryFilter | kTrySparse); tests switch it to 0 = walk only
+static uint32_t g_allow = rrt::kTryFilter | rrt::kTrySparse;
+
 extern "C" {
+
+void emu_set_allow(uint32_t allow) { g_allow = allow; }
 
 // v: n x 9 doubles; slow_div != 0 forces the true-division slab path (RRT_SLOW_DIV of the library)
 int emu_scene_create(const double* v, uint64_t n_tris, const double* root_min, const double* root_max,
@@ -98,6 +103,8 @@ int emu_scene_create(const double* v, uint64_t n_tris, const double* root_min, c
     s->dev.n_nodes = (uint32_t)s->flat.nodes.size();
     s->dev.root_tri_count = s->flat.n_stored ? 1u : 0u;                       // as rrt_scene_create (rrt_api.cu)
     s->dev.planes_safe = (s->flat.planes_safe && !slow_div) ? 1u : 0u;
+    s->dev.global_root = s->flat.global_root;
+    s->dev.sparse_ok = s->flat.sparse_ok ? 1u : 0u;
 #if RRT_CULL_F32
     s->dev.cull_o_max = rrt::kCullOriginRel * s->flat.scale;
 #else
@@ -158,14 +165,13 @@ int emu_ray_colours(void* p, const rrt_render_params* rp, uint64_t n, const doub
     const rrt::DevParams P = emu_params(rp, 1, 1, 0);
 #pragma omp parallel for schedule(dynamic, 256)
     for (long long i = 0; i < (long long)n; ++i) {
-        rrt::RayStateT<1> st;
+        rrt::RayState st;
         rrt::TraceCount tc;
         rrt::Hit h;
-        double park[rrt::kParkWords + 1];
         st.begin(rrt::V3{o[3 * i], o[3 * i + 1], o[3 * i + 2]}, rrt::V3{d[3 * i], d[3 * i + 1], d[3 * i + 2]});
         do {
-            rrt::traverse<false>(s->dev, st.so, st.sd, st.smax, st.shadow, h, tc);
-        } while (!st.advance<false>(s->dev, P, h, park));
+            rrt::traverse<false>(s->dev, st.so, st.sd, st.smax, st.shadow, h, tc, g_allow);
+        } while (!st.advance<false>(s->dev, P, h));
         const uint32_t c = st.res;
         out_rgb[3 * i] = (uint8_t)(c & 255u); out_rgb[3 * i + 1] = (uint8_t)((c >> 8) & 255u); out_rgb[3 * i + 2] = (uint8_t)((c >> 16) & 255u);
     }
@@ -199,14 +205,13 @@ int emu_render_shard(void* p, const rrt_render_params* rp, int tile_rows, int n_
             rrt::V3 d;
             uint32_t add;
             if (rrt::primary_ray(P, col, r, k, d)) {
-                rrt::RayStateT<1> st;
+                rrt::RayState st;
                 rrt::TraceCount tc;
                 rrt::Hit h;
-                double park[rrt::kParkWords + 1];
-                st.begin(rrt::V3{P.ox, P.oy, P.oz}, d);
+                        st.begin(rrt::V3{P.ox, P.oy, P.oz}, d);
                 do {
-                    rrt::traverse<false>(s->dev, st.so, st.sd, st.smax, st.shadow, h, tc);
-                } while (!st.advance<false>(s->dev, P, h, park));
+                    rrt::traverse<false>(s->dev, st.so, st.sd, st.smax, st.shadow, h, tc, g_allow);
+                } while (!st.advance<false>(s->dev, P, h));
                 if (hit_ids) hit_ids[pix * 4 + k] = st.hit0;
                 add = rrt::sample_add(st.res);
             } else {
@@ -231,7 +236,7 @@ int emu_trace_counts(void* p, uint64_t n, const double* o, const double* d, int 
         rrt::Hit h;
         rrt::TraceCount tc;
         rrt::traverse<true>(s->dev, rrt::V3{o[3 * i], o[3 * i + 1], o[3 * i + 2]}, rrt::V3{d[3 * i], d[3 * i + 1], d[3 * i + 2]},
-                            __longlong_as_double(0x7FF0000000000000ll), any_hit != 0, h, tc);
+                            __longlong_as_double(0x7FF0000000000000ll), any_hit != 0, h, tc, g_allow);
         mt += tc.mt; box += tc.box; cull += tc.cull; nodes += tc.nodes;
     }
     out[0] = mt; out[1] = box; out[2] = cull; out[3] = nodes;
@@ -248,7 +253,7 @@ int emu_trace_rays(void* p, uint64_t n, const double* o, const double* d, const 
         rrt::TraceCount tc;
         const rrt::V3 oo{o[3 * i], o[3 * i + 1], o[3 * i + 2]}, dd{d[3 * i], d[3 * i + 1], d[3 * i + 2]};
         const double mt = max_t ? max_t[i] : __longlong_as_double(0x7FF0000000000000ll);
-        rrt::traverse<false>(s->dev, oo, dd, mt, any_hit != 0, h, tc);
+        rrt::traverse<false>(s->dev, oo, dd, mt, any_hit != 0, h, tc, g_allow);
         out_tri[i] = (h.id == rrt::kNone) ? -1 : (int32_t)h.id;
         if (out_tuv) {
             out_tuv[3 * i] = out_tuv[3 * i + 1] = out_tuv[3 * i + 2] = 0.0;
@@ -262,20 +267,38 @@ int emu_trace_rays(void* p, uint64_t n, const double* o, const double* d, const 
     return 0;
 }
 
-// Closest accepted record of the WHOLE scene through the scene-wide culling hierarchy (flatten with RRT_GLOBAL_CULL=1),
+// what the searches did with n rays: out[0] = answered, out[1] = handed to the walk, out[2] = not tried
+int emu_search_outcomes(void* p, uint64_t n, const double* o, const double* d, const double* max_t, int any_hit, uint64_t* out) {
+    const EmuScene* s = static_cast<EmuScene*>(p);
+    uint64_t a = 0, h2 = 0, z = 0;
+#pragma omp parallel for schedule(dynamic, 256) reduction(+ : a, h2, z)
+    for (long long i = 0; i < (long long)n; ++i) {
+        rrt::Hit h;
+        rrt::TraceCount tc;
+        uint32_t oc = 0;
+        const double mt = max_t ? max_t[i] : __longlong_as_double(0x7FF0000000000000ll);
+        rrt::traverse<false>(s->dev, rrt::V3{o[3 * i], o[3 * i + 1], o[3 * i + 2]}, rrt::V3{d[3 * i], d[3 * i + 1], d[3 * i + 2]},
+                             mt, any_hit != 0, h, tc, g_allow, &oc);
+        a += oc == 1u; h2 += oc == 2u; z += oc == 0u;
+    }
+    out[0] = a; out[1] = h2; out[2] = z;
+    return 0;
+}
+
+// Closest accepted record of the WHOLE scene through the scene-wide culling hierarchy (flatten's global hierarchy),
 // ordered walk with limit pruning, ties to the smaller triangle id — i.e. a plain closest-hit tracer over the product's
 // records.  Development aid for the round-2 design note (profiles/r01_experiments.md): how often is that NOT what the
 // reference's octree walk returns?  out_tri[i] = id or -1; returns 1 when the scene has no scene-wide hierarchy.
 int emu_closest_global(void* p, uint64_t n, const double* o, const double* d, int32_t* out_tri) {
     const EmuScene* s = static_cast<EmuScene*>(p);
-    const uint32_t groot = s->dev.nodes[0]._pad2[0];
+    const uint32_t groot = s->dev.global_root;
     if (groot == 0u) return 1;
 #pragma omp parallel for schedule(dynamic, 256)
     for (long long i = 0; i < (long long)n; ++i) {
         const rrt::V3 oo{o[3 * i], o[3 * i + 1], o[3 * i + 2]}, dd{d[3 * i], d[3 * i + 1], d[3 * i + 2]};
         const rrt::AxisRay ax = rrt::make_axis(oo.x, dd.x, false), ay = rrt::make_axis(oo.y, dd.y, false),
                            az = rrt::make_axis(oo.z, dd.z, false);
-        const rrt::CullRay cr = rrt::make_cull_ray(s->dev, oo, dd, ax, ay, az);
+        const rrt::CullRay cr = rrt::make_cull_ray(s->dev.cull_o_max, oo, dd, ax, ay, az);
         rrt::Hit nb;
         nb.id = rrt::kNone; nb.rec = 0; nb.t = __longlong_as_double(0x7FF0000000000000ll);
         float limit = __int_as_float(0x7f800000);

@@ -18,7 +18,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 EMU_DIR = os.path.join(HERE, "host_emulation")
 EMU_SRC = os.path.join(EMU_DIR, "emu_trace.cpp")
-# RRT_EMU_FLAGS="-DRRT_SLAB_PRED=1 ...": the same tests over a compile-time VARIANT of the traversal headers (the flags a
+# RRT_EMU_FLAGS="-DFOO=1 ...": the same tests over a compile-time VARIANT of the traversal headers (the flags a
 # variant build of the library gets through RRT_EXTRA_FLAGS), in its own library file
 EMU_FLAGS = os.environ.get("RRT_EMU_FLAGS", "").split()
 EMU_LIB = os.path.join(EMU_DIR, "libemu_trace" + "".join(c if c.isalnum() else "_" for c in "".join(EMU_FLAGS)) + ".so")
@@ -61,6 +61,9 @@ def _load_emu(lib):
     L.emu_scene_set_shading.argtypes = [vp, C.c_uint64, vp, vp, vp, C.c_uint32, vp, C.c_uint32, vp]
     L.emu_ray_colours.argtypes = [vp, vp, C.c_uint64, vp, vp, vp]
     L.emu_render_shard.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp]
+    L.emu_set_allow.argtypes = [C.c_uint32]
+    L.emu_set_allow.restype = None
+    L.emu_search_outcomes.argtypes = [vp, C.c_uint64, vp, vp, vp, C.c_int, vp]
     return L
 
 
@@ -69,9 +72,10 @@ def emu():
     return _load_emu(_build_emu())
 
 
-# the compile-time experiments of rrt_trace.cuh prepared for round 2, all switched on together (profiles/r01_experiments.md)
-PREPARED_VARIANTS = ["-DRRT_SLAB_PRED=1", "-DRRT_LATE_PRUNE=1", "-DRRT_CULL_LOOP=3", "-DRRT_PEND=2", "-DRRT_SHADOW_FILTER=1",
-                     "-DRRT_PRIMARY_FILTER=1"]
+# By default the emulation lets traverse() try BOTH searches of the scene-wide hierarchy on every ray they apply to
+# (rrt_trace.cuh: scene_clear on any-hit rays, sparse_closest on closest-hit rays with max_t = inf — also on rays from
+# inside the geometry, which the render kernel leaves to the walk): the whole suite fuzzes their hand-over rules.
+ALLOW_ALL, ALLOW_WALK_ONLY = 3, 0
 
 
 class EmuScene:
@@ -387,28 +391,34 @@ def test_shards_through_the_kernel_helpers(emu, rrt, scenes, W, H, T, G):
     osc.close()
 
 
-@pytest.mark.parametrize("global_cull", [False, True])
-def test_prepared_variants_stay_exact(rrt, scenes, monkeypatch, global_cull):
-    # The experiment switches of the traversal (children hit mask from pairwise quotient comparisons, queued leaves, late
-    # pruning, the any-accepted-hit filter on every ray) must keep returning the oracle's answers: a smaller fuzz run and
-    # one whole frame over a library built with all of them on, so that they cannot rot unnoticed between GPU sessions.
+def test_walk_only_and_search_outcomes(emu, rrt, scenes):
+    # the same answers with the searches switched off (RRT_SEARCH_MODE=0: the pure octree walk), and the searches do
+    # answer most of the rays they are meant for: camera rays of the teapot scene, shadow-like rays towards a light
     from oracle.oracle import OracleScene
-    flags = list(PREPARED_VARIANTS)
-    if global_cull:   # the filter over one scene-wide culling hierarchy, which flatten builds on request
-        flags[flags.index("-DRRT_SHADOW_FILTER=1")] = "-DRRT_SHADOW_FILTER=2"
-        flags.append("-DRRT_SPARSE_PRIMARY=1")   # closest-hit rays answered from that hierarchy where provably the same
-        monkeypatch.setenv("RRT_GLOBAL_CULL", "1")
-    L = _load_emu(_build_emu(flags))
     sd = scenes("model2")
     rng = np.random.default_rng(77)
     o, d, mt = fuzz_rays(rng, 120_000, np.array([0.0, 3.0, 0.0]), 9.0)
     o[1::29] = np.array([0.0, 2.0, -10.0])
     osc = OracleScene(sd)
-    es = EmuScene(L, sd)
-    check(es, osc, o, d, mt, min_hits=9_000)
-    p = rrt.make_params(96, 54)
-    fb, hit = es.render_shard(p)
-    ofb, ohit, _, _ = osc.render(p)
-    assert np.array_equal(hit, ohit) and np.array_equal(fb, ofb)
+    es = EmuScene(emu, sd)
+    try:
+        emu.emu_set_allow(ALLOW_WALK_ONLY)
+        check(es, osc, o, d, mt, min_hits=9_000)
+        p = rrt.make_params(96, 54)
+        fb, hit = es.render_shard(p)
+        ofb, ohit, _, _ = osc.render(p)
+        assert np.array_equal(hit, ohit) and np.array_equal(fb, ofb)
+    finally:
+        emu.emu_set_allow(ALLOW_ALL)
+    # camera rays (engine.rs:207-211): direction (x/W, y/H, 1) from (0, 2, -10)
+    n = 40_000
+    cam_o = np.tile(np.array([0.0, 2.0, -10.0]), (n, 1))
+    cam_d = np.stack([rng.uniform(-0.5, 0.5, n), rng.uniform(-0.5, 0.5, n), np.ones(n)], 1)
+    out = np.zeros(3, dtype=np.uint64)
+    assert emu.emu_search_outcomes(es.h, n, cam_o.ctypes.data, cam_d.ctypes.data, None, 0, out.ctypes.data) == 0
+    assert out[2] == 0 and out[0] > 0.8 * n, out          # tried on every ray, answers most of them
+    tri, _ = es.trace(cam_o, cam_d)
+    otri, _ = osc.trace(cam_o, cam_d)
+    assert np.array_equal(tri, otri) and (tri >= 0).mean() > 0.3
     es.close()
     osc.close()

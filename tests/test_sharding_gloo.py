@@ -121,3 +121,61 @@ def test_owned_frames_partition():
             assert max(len(p) for p in parts) - min(len(p) for p in parts) <= 1
     one = np.stack([_frame_pattern(k, 6, 4) for k in range(3)])
     assert np.array_equal(gather_frames(one, 3, 0, 1), one)       # world 1: no process group needed
+
+
+# ---------------------------------------------------------------- the shared host canvas (rrt_host_frame_*, no GPU needed)
+def _host_frame_worker(rank, world, name, W, H, T, q):
+    sys.path.insert(0, ROOT)
+    import rrt_b200  # noqa: F401
+    from rrt_b200 import abi
+    from rrt_b200.sharding import HostFrame, ShardedRenderer, owned_rows  # noqa: F401  (import check of the N>1 classes)
+    import ctypes as C
+    hf = HostFrame(name, W, H, world, create=(rank == 0))           # no device: not page-locked, same protocol
+    rows = owned_rows(H, T, world, rank)
+    ok = True
+    for frame in range(3):
+        if frame:
+            hf.barrier(30.0)                                         # "rank 0 is done reading the previous frame"
+        hf.pixels[rows] = _pattern(rows, W) + frame                  # stands in for this rank's device->host row copies
+        hf.barrier(30.0)                                             # "frame complete"
+        if rank == 0:
+            expect = _pattern(range(H), W) + frame
+            ok = ok and bool(np.array_equal(hf.pixels, expect))
+    # the CUDA IPC handle slot of the header: rank 0 publishes 64 bytes, the others fetch them
+    L = abi.lib()
+    buf = (C.c_ubyte * 64)()
+    if rank == 0:
+        for i in range(64):
+            buf[i] = (i * 7 + 3) & 255
+        abi.check(L.rrt_host_frame_publish_handle(hf._h, buf))
+    else:
+        abi.check(L.rrt_host_frame_fetch_handle(hf._h, 30.0, buf))
+        ok = ok and bytes(buf) == bytes((i * 7 + 3) & 255 for i in range(64))
+    hf.barrier(30.0)
+    hf.close()
+    q.put((rank, ok))
+
+
+@pytest.mark.parametrize("world,W,H,T", [(2, 64, 45, 8), (3, 40, 50, 4)])
+def test_shared_host_frame_barrier_and_handle_slot(world, W, H, T):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    name = f"/rrt_test_{os.getpid()}_{world}"
+    ps = [ctx.Process(target=_host_frame_worker, args=(r, world, name, W, H, T, q)) for r in range(world)]
+    for p in ps:
+        p.start()
+    res = [q.get(timeout=120) for _ in range(world)]
+    for p in ps:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert all(ok for _, ok in res)
+    assert not os.path.exists("/dev/shm" + name)                     # the creator unlinked the segment
+
+
+def test_host_frame_barrier_times_out_instead_of_hanging(rrt):
+    from rrt_b200.sharding import HostFrame
+    hf = HostFrame(f"/rrt_test_timeout_{os.getpid()}", 8, 4, 2, create=True)    # 2 ranks expected, 1 present
+    with pytest.raises(Exception) as ei:
+        hf.barrier(0.3)
+    assert "timeout" in str(ei.value)
+    hf.close()

@@ -73,6 +73,12 @@ prof[workload + "_fp64_lane_inst"] = float(fp64_lane)
 prof[workload + "_warp_inst"] = float(warp_inst)
 prof[workload + "_issue_active_pct"] = float(raw["smsp__issue_active.avg.pct_of_peak_sustained_active"][1])
 prof[workload + "_fp64_pipe_active_pct"] = float(raw["sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active"][1])
+prof[workload + "_avg_active_lanes"] = float(raw["smsp__thread_inst_executed_per_inst_executed.ratio"][1])
+prof[workload + "_kernel_ms_under_ncu"] = float(raw["gpu__time_duration.sum"][1]) * {"ms": 1.0, "us": 1e-3, "s": 1e3, "ns": 1e-6}.get(raw["gpu__time_duration.sum"][0], 1.0)
+try:   # the capture is assumed to be of the library as built now (tools/r02_*.sh profile right after building)
+    prof[workload + "_kernel_id"] = open(os.path.join(ROOT, "rust-ray-tracer_b200", "csrc", "librrt_b200.kernel_id")).read().strip()
+except OSError:
+    prof[workload + "_kernel_id"] = None
 prof[workload + "_source"] = os.path.relpath(out_path, ROOT)
 prof["source"] = ("per workload: <w> = dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of render_kernel (ncu --set full); "
                   "<w>_fp64_lane_inst = sum over DADD/DMUL/DFMA/DSETP of thread instructions executed; see <w>_source")
