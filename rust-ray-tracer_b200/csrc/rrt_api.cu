@@ -67,6 +67,8 @@ struct rrt_scene {
     size_t fb_cap = 0, hit_cap = 0, scratch_cap = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     RenderSchedule sched;            // dispatch order of the next frame from the measured cost of this one (rrt_render.h)
+    WaveBuffers wave;                // state arrays + queues of the wavefront renderer (rrt_render.h)
+    bool wavefront = true;           // RRT_RENDERER=mega at scene creation: the persistent single kernel of round 1
     uint32_t* d_fstat = nullptr;     // what the searches round the walk returned last frame + their switches (DevParams::fstat)
     int search_mode = 1;             // RRT_SEARCH_MODE at scene creation: 0 walk only, 1 switched per frame (default), 2 always
     // rrt_render_frames: two device frames, a render and a copy stream, created on first use
@@ -93,6 +95,7 @@ struct rrt_scene {
         if (d_hit) cudaFree(d_hit);
         if (d_scratch) cudaFree(d_scratch);
         if (d_fstat) cudaFree(d_fstat);
+        wave.release();
         sched.release();
         if (seq_render) { cudaStreamSynchronize(seq_render); cudaStreamDestroy(seq_render); }
         if (seq_copy) { cudaStreamSynchronize(seq_copy); cudaStreamDestroy(seq_copy); }
@@ -237,6 +240,9 @@ int rrt_scene_create(const rrt_scene_desc* d, int device, rrt_scene** out) {
 
     auto sc = std::make_unique<rrt_scene>();
     sc->search_mode = search_mode;
+    if (const char* e = std::getenv("RRT_RENDERER")) sc->wavefront = std::string(e) != "mega";
+    for (uint32_t i = 0; i < d->n_materials; ++i)
+        if (d->materials[i].kr > 0.0) sc->wave.scene_has_mirrors = true;
     sc->device = device;
     if (const char* e = getenv("RRT_ORDER_HINT")) sc->sched.enabled = atoi(e) != 0;
     if (const char* e = getenv("RRT_ORDER_TAIL")) sc->sched.tail_safety = (float)atof(e);   // tuning knob (rrt_render.h)
@@ -368,6 +374,13 @@ int ensure(T** p, size_t* cap, size_t n) {
     return RRT_OK;
 }
 
+// one frame (or shard) of Scene::draw_scene on `stream`: the wavefront of kernels, or the single persistent kernel
+cudaError_t render_frame(rrt_scene* s, const DevParams& P, uint32_t* d_fb, int32_t* d_hit, DevCounters* d_counters,
+                         cudaStream_t stream) {
+    if (s->wavefront) return launch_wavefront(s->dev, P, d_fb, d_hit, s->d_scratch, d_counters, stream, &s->wave);
+    return launch_render(s->dev, P, d_fb, d_hit, s->d_scratch, d_counters, stream, d_counters ? nullptr : &s->sched);
+}
+
 struct DevBuf {  // RAII scratch for the per-ray seams
     void* p = nullptr;
     ~DevBuf() { if (p) cudaFree(p); }
@@ -389,7 +402,7 @@ int rrt_render_device(rrt_scene* s, const rrt_render_params* p, const rrt_shard*
     if (rc) return rc;
     CU(cudaSetDevice(s->device));
     if ((rc = ensure(&s->d_scratch, &s->scratch_cap, render_scratch_words(P.n_rows_local, P.W)))) return rc;
-    CU(launch_render(s->dev, P, d_fb, d_hit_ids, s->d_scratch, nullptr, (cudaStream_t)cuda_stream, &s->sched));
+    CU(render_frame(s, P, d_fb, d_hit_ids, nullptr, (cudaStream_t)cuda_stream));
     return RRT_OK;
 }
 
@@ -402,7 +415,7 @@ int rrt_render_device_into_frame(rrt_scene* s, const rrt_render_params* p, const
     P.full_frame = 1;
     CU(cudaSetDevice(s->device));
     if ((rc = ensure(&s->d_scratch, &s->scratch_cap, render_scratch_words(P.n_rows_local, P.W)))) return rc;
-    CU(launch_render(s->dev, P, d_frame, nullptr, s->d_scratch, nullptr, (cudaStream_t)cuda_stream, &s->sched));
+    CU(render_frame(s, P, d_frame, nullptr, nullptr, (cudaStream_t)cuda_stream));
     return RRT_OK;
 }
 
@@ -465,7 +478,7 @@ int rrt_render_to_host_frame(rrt_scene* s, const rrt_render_params* p, const rrt
     const size_t n = (size_t)P.W * std::max(P.n_rows_local, 1);
     if ((rc = ensure(&s->d_fb, &s->fb_cap, n))) return rc;
     if ((rc = ensure(&s->d_scratch, &s->scratch_cap, render_scratch_words(P.n_rows_local, P.W)))) return rc;
-    CU(launch_render(s->dev, P, s->d_fb, nullptr, s->d_scratch, nullptr, st, &s->sched));
+    CU(render_frame(s, P, s->d_fb, nullptr, nullptr, st));
     const size_t row_bytes = (size_t)P.W * sizeof(uint32_t), group = row_bytes * P.tile_rows;
     const int n_full = P.n_rows_local / P.tile_rows, rest = P.n_rows_local % P.tile_rows;
     uint32_t* dst0 = host_frame + (size_t)P.shard_index * P.tile_rows * P.W;
@@ -488,7 +501,7 @@ int rrt_render(rrt_scene* s, const rrt_render_params* p, uint32_t* fb, int32_t* 
     if (hit_ids && (rc = ensure(&s->d_hit, &s->hit_cap, n * 4))) return rc;
     if ((rc = ensure(&s->d_scratch, &s->scratch_cap, render_scratch_words(P.n_rows_local, P.W)))) return rc;
     CU(cudaEventRecord(s->ev0, 0));
-    CU(launch_render(s->dev, P, s->d_fb, hit_ids ? s->d_hit : nullptr, s->d_scratch, nullptr, 0, &s->sched));
+    CU(render_frame(s, P, s->d_fb, hit_ids ? s->d_hit : nullptr, nullptr, 0));
     CU(cudaEventRecord(s->ev1, 0));
     CU(cudaMemcpy(fb, s->d_fb, n * sizeof(uint32_t), cudaMemcpyDeviceToHost));
     if (hit_ids) CU(cudaMemcpy(hit_ids, s->d_hit, n * 4 * sizeof(int32_t), cudaMemcpyDeviceToHost));
@@ -528,7 +541,7 @@ int rrt_render_frames(rrt_scene* s, const rrt_render_params* params, int32_t n_f
             if ((rc = ensure(&s->d_seq_fb[b], &s->seq_cap[b], n))) return rc;   // no-op after the first two frames
             if ((rc = ensure(&s->d_scratch, &s->scratch_cap, render_scratch_words(P.n_rows_local, P.W)))) return rc;
             if (i >= 2) CU(cudaStreamWaitEvent(s->seq_render, s->seq_copied[b], 0));   // frame i-2 has left this buffer
-            CU(launch_render(s->dev, P, s->d_seq_fb[b], nullptr, s->d_scratch, nullptr, s->seq_render, &s->sched));
+            CU(render_frame(s, P, s->d_seq_fb[b], nullptr, nullptr, s->seq_render));
             CU(cudaEventRecord(s->seq_rendered[b], s->seq_render));
             CU(cudaStreamWaitEvent(s->seq_copy, s->seq_rendered[b], 0));
             CU(cudaMemcpyAsync(fbs[i], s->d_seq_fb[b], n * sizeof(uint32_t), cudaMemcpyDeviceToHost, s->seq_copy));
@@ -571,7 +584,7 @@ int rrt_render_counters(rrt_scene* s, const rrt_render_params* p, uint32_t* fb, 
     if ((rc = c.alloc(sizeof(DevCounters)))) return rc;
     CU(cudaMemset(c.p, 0, sizeof(DevCounters)));
     if ((rc = ensure(&s->d_scratch, &s->scratch_cap, render_scratch_words(P.n_rows_local, P.W)))) return rc;
-    CU(launch_render(s->dev, P, s->d_fb, nullptr, s->d_scratch, (DevCounters*)c.p, 0));
+    CU(render_frame(s, P, s->d_fb, nullptr, (DevCounters*)c.p, 0));
     DevCounters h;
     CU(cudaMemcpy(&h, c.p, sizeof h, cudaMemcpyDeviceToHost));
     if (fb) CU(cudaMemcpy(fb, s->d_fb, n * sizeof(uint32_t), cudaMemcpyDeviceToHost));

@@ -160,16 +160,28 @@ def _peer_worker(rank, world, port, q):
     sd = load_scene_npz(os.path.join(os.path.dirname(__file__), "golden", "scenes", "model2.npz"))
     rt = rrt_b200.RayTracer(sd, device=rank)
     W, H = 640, 360
-    p = rt.params(W, H)
+    # a MOVING camera: every frame differs, so a frame torn between two renders (a rank storing frame k+1 while rank 0
+    # still reads frame k) cannot go unnoticed
+    cams = []
+    for k in (0, 3, 7, 12, 18, 25):
+        origin, rot = rrt_b200.orbit_camera(k)
+        cams.append(rt.params(W, H, origin=origin, camera_rot=rot))
     out = {}
-    for mode in ("peer", "nccl"):
+    for mode in ("peer", "nccl", "host"):
         sr = ShardedRenderer(rt, W, H, rank, world, tile_rows=8, assemble=mode)
-        for _ in range(2):
+        frames = []
+        host = torch.empty((len(cams), H, W), dtype=torch.int32, pin_memory=True)
+        for i, p in enumerate(cams):
             sr.render(p)
             f = sr.assemble()
+            if rank == 0:
+                if mode == "host":
+                    frames.append(np.array(f, dtype=np.uint32, copy=True))      # read before the next render() call
+                else:
+                    host[i].copy_(f, non_blocking=True)                           # consumed ON the render stream
         torch.cuda.synchronize()
         if rank == 0:
-            out[mode] = f.cpu().numpy().view(np.uint32).copy()
+            out[mode] = frames if mode == "host" else [host[i].numpy().view(np.uint32).copy() for i in range(len(cams))]
         if rank != 0:
             sr.close()
         dist.barrier()
@@ -177,7 +189,8 @@ def _peer_worker(rank, world, port, q):
             sr.close()
     if rank == 0:
         sc = rrt_b200.Scene(W, H)
-        out["whole"] = sc.draw_scene(rt).copy()
+        out["whole"] = [sc.draw_scene(rt, origin=tuple(p.origin), camera_rot=(np.array(p.camera_rot).reshape(3, 3) if p.use_camera_rot else None)).copy()
+                        for p in cams]
         q.put(out)
     rt.close()
     dist.barrier()
@@ -185,7 +198,9 @@ def _peer_worker(rank, world, port, q):
 
 
 def test_peer_frame_two_gpus(rrt):
-    # N = 2, one process per GPU: rank 1's render kernel stores into rank 0's frame through CUDA IPC / NVLink
+    # N = 2, one process per GPU, a moving camera: rank 1's render kernel stores into rank 0's frames through CUDA IPC /
+    # NVLink (two frames used alternately), the NCCL all-gather mode, and the shared page-locked HOST frame every rank
+    # copies its rows into — each of the six frames must equal the single-GPU frame of the same camera
     import torch
     import torch.multiprocessing as mp
     if torch.cuda.device_count() < 2:
@@ -199,7 +214,29 @@ def test_peer_frame_two_gpus(rrt):
     for pr in procs:
         pr.join(timeout=120)
         assert pr.exitcode == 0
-    assert np.array_equal(out["peer"], out["whole"]) and np.array_equal(out["nccl"], out["whole"])
+    assert any(not np.array_equal(out["whole"][0], w) for w in out["whole"][1:])
+    for mode in ("peer", "nccl", "host"):
+        for i, w in enumerate(out["whole"]):
+            assert np.array_equal(out[mode][i], w), (mode, i)
+
+
+def test_host_frame_single_rank_equals_rrt_render(rrt, scenes):
+    # rrt_render_to_host_frame with one shard, and with the shards of a 3-way split rendered one after another into one
+    # host frame (pitched copies of whole tile-row groups + the ragged last group): the frame rrt_render gives
+    import torch
+    sd = scenes("model2")
+    rt = rrt.RayTracer(sd)
+    L = rrt.abi.lib()
+    for W, H, G, T in ((640, 360, 1, 8), (333, 101, 3, 8), (200, 57, 2, 5)):
+        p = rt.params(W, H)
+        whole = rrt.Scene(W, H).draw_scene(rt).copy()
+        host = torch.zeros((H, W), dtype=torch.int32, pin_memory=True)
+        for r in range(G):
+            sh = rrt.abi.Shard(T, G, r)
+            rrt.abi.check(L.rrt_render_to_host_frame(rt.handle, C.byref(p), C.byref(sh), host.data_ptr(), None))
+            torch.cuda.synchronize()
+        assert np.array_equal(host.numpy().view(np.uint32), whole), (W, H, G, T)
+    rt.close()
 
 
 def test_order_hint_changes_nothing(rrt, scenes):
