@@ -11,7 +11,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.environ.get("RRT_OUT") or os.path.join(CSRC, "librrt_b200.so")   # RRT_OUT: variant builds (tools/)
-SOURCES = ["rrt_api.cu", "rrt_render.cu", "rrt_wavefront.cu", "rrt_microbench.cu", "rrt_hostframe.cu", "rrt_octree.cpp", "rrt_loader.cpp"]
+SOURCES = ["rrt_api.cu", "rrt_render.cu", "rrt_microbench.cu", "rrt_hostframe.cu", "rrt_octree.cpp", "rrt_loader.cpp"]
 HEADERS = ["rrt_device.cuh", "rrt_trace.cuh", "rrt_shade.cuh", "rrt_raygen.cuh", "rrt_render.h", "rrt_octree.h",
            os.path.join("..", "..", "include", "rrt.h")]
 
@@ -56,7 +56,7 @@ def build(force=False, verbose=False):
     # (bench.py reports it next to the kernel id of the committed ncu capture it takes its roofline counts from)
     import hashlib
     h = hashlib.sha1(" ".join(NVCC_FLAGS + os.environ.get("RRT_EXTRA_FLAGS", "").split()).encode())
-    for f in ["rrt_render.cu", "rrt_wavefront.cu", "rrt_device.cuh", "rrt_trace.cuh", "rrt_shade.cuh", "rrt_raygen.cuh", "rrt_octree.h"]:
+    for f in ["rrt_render.cu", "rrt_device.cuh", "rrt_trace.cuh", "rrt_shade.cuh", "rrt_raygen.cuh", "rrt_octree.h"]:
         h.update(open(os.path.join(CSRC, f), "rb").read())
     with open(OUT[:-3] + ".kernel_id", "w") as f:
         f.write(h.hexdigest()[:16] + "\n")

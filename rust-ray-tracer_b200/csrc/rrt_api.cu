@@ -67,8 +67,6 @@ struct rrt_scene {
     size_t fb_cap = 0, hit_cap = 0, scratch_cap = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     RenderSchedule sched;            // dispatch order of the next frame from the measured cost of this one (rrt_render.h)
-    WaveBuffers wave;                // state arrays + queues of the wavefront renderer (rrt_render.h)
-    bool wavefront = true;           // RRT_RENDERER=mega at scene creation: the persistent single kernel of round 1
     uint32_t* d_fstat = nullptr;     // what the searches round the walk returned last frame + their switches (DevParams::fstat)
     int search_mode = 1;             // RRT_SEARCH_MODE at scene creation: 0 walk only, 1 switched per frame (default), 2 always
     // rrt_render_frames: two device frames, a render and a copy stream, created on first use
@@ -95,7 +93,6 @@ struct rrt_scene {
         if (d_hit) cudaFree(d_hit);
         if (d_scratch) cudaFree(d_scratch);
         if (d_fstat) cudaFree(d_fstat);
-        wave.release();
         sched.release();
         if (seq_render) { cudaStreamSynchronize(seq_render); cudaStreamDestroy(seq_render); }
         if (seq_copy) { cudaStreamSynchronize(seq_copy); cudaStreamDestroy(seq_copy); }
@@ -240,9 +237,6 @@ int rrt_scene_create(const rrt_scene_desc* d, int device, rrt_scene** out) {
 
     auto sc = std::make_unique<rrt_scene>();
     sc->search_mode = search_mode;
-    if (const char* e = std::getenv("RRT_RENDERER")) sc->wavefront = std::string(e) != "mega";
-    for (uint32_t i = 0; i < d->n_materials; ++i)
-        if (d->materials[i].kr > 0.0) sc->wave.scene_has_mirrors = true;
     sc->device = device;
     if (const char* e = getenv("RRT_ORDER_HINT")) sc->sched.enabled = atoi(e) != 0;
     if (const char* e = getenv("RRT_ORDER_TAIL")) sc->sched.tail_safety = (float)atof(e);   // tuning knob (rrt_render.h)
@@ -374,10 +368,9 @@ int ensure(T** p, size_t* cap, size_t n) {
     return RRT_OK;
 }
 
-// one frame (or shard) of Scene::draw_scene on `stream`: the wavefront of kernels, or the single persistent kernel
+// one frame (or shard) of Scene::draw_scene on `stream`
 cudaError_t render_frame(rrt_scene* s, const DevParams& P, uint32_t* d_fb, int32_t* d_hit, DevCounters* d_counters,
                          cudaStream_t stream) {
-    if (s->wavefront) return launch_wavefront(s->dev, P, d_fb, d_hit, s->d_scratch, d_counters, stream, &s->wave);
     return launch_render(s->dev, P, d_fb, d_hit, s->d_scratch, d_counters, stream, d_counters ? nullptr : &s->sched);
 }
 
@@ -558,19 +551,6 @@ int rrt_render_frames(rrt_scene* s, const rrt_render_params* params, int32_t n_f
     if (total_ms) CU(cudaEventElapsedTime(total_ms, s->seq_t0, s->seq_t1));
     return RRT_OK;
 }
-
-#if defined(RRT_PROBE) && RRT_PROBE
-extern "C" int rrt_debug_probe(const DevScene*, const DevParams*, int, int, int, float*, unsigned long long*);
-// experiment builds only (tools/probe.py)
-int rrt_debug_probe_scene(rrt_scene* s, const rrt_render_params* p, int kind, int mode, int reps, float* ms,
-                          unsigned long long* out) {
-    DevParams P;
-    int rc = make_params(s, p, nullptr, &P);
-    if (rc) return rc;
-    CU(cudaSetDevice(s->device));
-    return rrt_debug_probe(&s->dev, &P, kind, mode, reps, ms, out);
-}
-#endif
 
 int rrt_render_counters(rrt_scene* s, const rrt_render_params* p, uint32_t* fb, rrt_counters* out) {
     if (!s || !out) return fail(RRT_ERR_INVALID, "null argument");

@@ -289,89 +289,6 @@ __global__ void iota_kernel(uint32_t* __restrict__ v, uint32_t n) {
     if (i < n) v[i] = i;
 }
 
-#ifndef RRT_PROBE
-#define RRT_PROBE 0
-#endif
-#if RRT_PROBE
-// ---------------------------------------------------------------- experiment builds only (-DRRT_PROBE=1)
-// What would each kind of traversal cost as a kernel of its own (own register budget, every lane on the same kind of
-// ray)?  probe_fill writes one ray per sample — kind 0: the camera ray, kind 1: the ray the shading state machine asks
-// for next after the camera ray's hit (light 1's shadow query, or the mirror ray) — and probe_trace runs ONE traversal
-// flavour over the buffer.  Not product code: tools/probe.py drives it, profiles/r02_experiments.md has the numbers.
-struct ProbeRay { double ox, oy, oz, dx, dy, dz, max_t; uint32_t kind, _pad; };   // kind: 0 none, 1 closest hit, 2 any hit
-
-__global__ void __launch_bounds__(kBlock)
-probe_fill_kernel(const DevScene sc, const __grid_constant__ DevParams P, ProbeRay* __restrict__ rays, const int tiles_x,
-                  const unsigned long long total, const int kind) {
-    const unsigned long long s = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= total) return;
-    ProbeRay r{};
-    const unsigned long long tile = s >> 5;
-    int col, krow;
-    unsigned k;
-    sample_pixel(tile >> 3, (unsigned)tile & 7u, (unsigned)s & 31u, tiles_x, col, krow, k);
-    V3 d;
-    if (col < P.W && krow < P.n_rows_local && primary_ray(P, col, buffer_row(P, krow), k, d)) {
-        if (kind == 0) {
-            r = ProbeRay{P.ox, P.oy, P.oz, d.x, d.y, d.z, __longlong_as_double(0x7FF0000000000000ll), 1u, 0u};
-        } else {
-            RayState st;
-            st.begin(V3{P.ox, P.oy, P.oz}, d);
-            Hit h;
-            TraceCount tc;
-            traverse<false>(sc, st.so, st.sd, st.smax, false, h, tc, 0u);
-            if (!st.advance<false>(sc, P, h))
-                r = ProbeRay{st.so.x, st.so.y, st.so.z, st.sd.x, st.sd.y, st.sd.z, st.smax, st.shadow ? 2u : 1u, 0u};
-        }
-    }
-    rays[s] = r;
-}
-
-#ifndef RRT_PROBE_MIN_BLOCKS
-#define RRT_PROBE_MIN_BLOCKS 1
-#endif
-// mode 0: the exact octree walk; mode 1: only the search that goes round it (sparse_closest for closest-hit rays,
-// shadow_clear for any-hit rays) — rays it cannot answer are COUNTED, not walked
-template <int MODE>
-__global__ void __launch_bounds__(kBlock, RRT_PROBE_MIN_BLOCKS)
-probe_trace_kernel(const DevScene sc, const ProbeRay* __restrict__ rays, const unsigned long long total,
-                   unsigned long long* __restrict__ out) {
-    const unsigned long long s = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
-    unsigned long long n_rays = 0, n_answered = 0, sum = 0;
-    if (s < total) {
-        const ProbeRay r = rays[s];
-        if (r.kind != 0u) {
-            n_rays = 1;
-            const V3 o{r.ox, r.oy, r.oz}, d{r.dx, r.dy, r.dz};
-            Hit h;
-            h.id = kNone; h.rec = 0; h.t = r.max_t;
-            TraceCount tc;
-            if (MODE == 0) {
-                traverse<false>(sc, o, d, r.max_t, r.kind == 2u, h, tc, 0u);
-                n_answered = 1;
-            } else if (r.kind == 2u) {
-                n_answered = scene_clear<false>(search_scene(sc), o, d, r.max_t, tc) ? 1 : 0;
-            } else {
-                const SparseResult sr = sparse_closest<false>(search_scene(sc), o, d, tc);
-                n_answered = sr.status;
-                h.id = sr.id;
-            }
-            sum = h.id;
-        }
-    }
-    for (int o = 16; o > 0; o >>= 1) {
-        n_rays += __shfl_xor_sync(0xFFFFFFFFu, n_rays, o);
-        n_answered += __shfl_xor_sync(0xFFFFFFFFu, n_answered, o);
-        sum += __shfl_xor_sync(0xFFFFFFFFu, sum, o);
-    }
-    if ((threadIdx.x & 31u) == 0u) {
-        if (n_rays) atomicAdd(out, n_rays);
-        if (n_answered) atomicAdd(out + 1, n_answered);
-        if (sum) atomicAdd(out + 2, sum);
-    }
-}
-#endif
-
 }  // namespace
 
 void RenderSchedule::release() {
@@ -516,43 +433,6 @@ extern "C" int rrt_debug_timeline(unsigned long long* out, int reset) {
 }
 #endif
 
-#if RRT_PROBE
-// experiment builds only: out[0..2] = rays, answered, checksum; ms[0] = fill, ms[1] = trace (CUDA events)
-extern "C" int rrt_debug_probe(const DevScene* scp, const DevParams* Pp, int kind, int mode, int reps, float* ms,
-                               unsigned long long* out) {
-    const DevScene& sc = *scp;
-    const DevParams& P = *Pp;
-    const int tiles_x = (P.W + kTileW - 1) / kTileW, tiles_y = (P.n_rows_local + kTileH - 1) / kTileH;
-    const unsigned long long total = (unsigned long long)tiles_x * tiles_y * (kTileW * kTileH * 4);
-    ProbeRay* rays = nullptr;
-    unsigned long long* d_out = nullptr;
-    if (cudaMalloc(&rays, total * sizeof(ProbeRay)) != cudaSuccess || cudaMalloc(&d_out, 24) != cudaSuccess) return 1;
-    cudaEvent_t e0, e1, e2;
-    cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventCreate(&e2);
-    const unsigned grid = (unsigned)((total + kBlock - 1) / kBlock);
-    cudaEventRecord(e0);
-    probe_fill_kernel<<<grid, kBlock>>>(sc, P, rays, tiles_x, total, kind);
-    cudaEventRecord(e1);
-    float best = 1e30f;
-    for (int i = 0; i < reps; ++i) {
-        cudaMemset(d_out, 0, 24);
-        cudaEventRecord(e1);
-        if (mode == 0) probe_trace_kernel<0><<<grid, kBlock>>>(sc, rays, total, d_out);
-        else probe_trace_kernel<1><<<grid, kBlock>>>(sc, rays, total, d_out);
-        cudaEventRecord(e2);
-        if (cudaEventSynchronize(e2) != cudaSuccess) return 2;
-        float t = 0;
-        cudaEventElapsedTime(&t, e1, e2);
-        best = t < best ? t : best;
-    }
-    cudaEventElapsedTime(&ms[0], e0, e1);
-    ms[1] = best;
-    cudaMemcpy(out, d_out, 24, cudaMemcpyDeviceToHost);
-    cudaFree(rays); cudaFree(d_out);
-    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2);
-    return cudaGetLastError() == cudaSuccess ? 0 : 3;
-}
-#endif
 
 size_t render_scratch_words(int n_rows_local, int W) { return (((size_t)n_rows_local * W + 1) & ~(size_t)1) + 2; }
 

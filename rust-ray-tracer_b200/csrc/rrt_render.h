@@ -31,23 +31,6 @@ struct RenderSchedule {
     void release();
 };
 
-// Device memory of the wavefront renderer (rrt_wavefront.cu), per scene handle, grown on demand: slot-indexed state of
-// the samples in flight + three queues of slots.
-struct WaveBuffers {
-    void* base = nullptr;
-    uint32_t* h_cnt = nullptr;       // pinned: queue lengths read back between ray levels
-    uint32_t cap_slots = 0;
-    int mirror_levels = 0;           // open mirror levels the state arrays can hold (0: the scene has no mirrors)
-    bool scene_has_mirrors = false;  // set at scene creation: some material has Kr > 0
-    size_t bytes = 0;
-    void release();
-    ~WaveBuffers();
-};
-// Scene::draw_scene as a wavefront of kernels.  d_acc: n_rows_local * W u32 words (per-pixel accumulators, zeroed here).
-// Asynchronous on `stream` for scenes without mirrors; with mirrors it synchronises the stream once per ray level.
-cudaError_t launch_wavefront(const DevScene& sc, const DevParams& P, uint32_t* d_fb, int32_t* d_hit, uint32_t* d_acc,
-                             DevCounters* d_counters, cudaStream_t stream, WaveBuffers* wb);
-
 // d_scratch: render_scratch_words(P.n_rows_local, P.W) u32 words of device memory (zeroed by the launcher)
 cudaError_t launch_render(const DevScene& sc, const DevParams& P, uint32_t* d_fb, int32_t* d_hit, uint32_t* d_scratch,
                           DevCounters* d_counters, cudaStream_t stream, RenderSchedule* sch = nullptr);

@@ -83,3 +83,43 @@ def rgb_planes(fb):
 def has_gpu():
     import rrt_b200
     return rrt_b200.abi.lib().rrt_device_count() > 0
+
+
+def grazing_rays(sd, n, rng, eps_lo=1e-16, eps_hi=1e-8):
+    """Adversarial rays for the conservative f32 culling: every ray runs IN the plane of a scene
+    triangle or within |eps| rad of it (|eps| log-uniform in [eps_lo, eps_hi]) and is aimed at a point of that triangle,
+    so that the reference's determinant `a` (ray.rs:64) sweeps from rounding noise to 1e-8 relative.
+    -> origins, directions, index of the triangle each ray was built on."""
+    v = np.asarray(sd.v, dtype=np.float64).reshape(-1, 3, 3)
+    tri = rng.integers(0, len(v), n)
+    a, b, c = v[tri, 0], v[tri, 1], v[tri, 2]
+    e1, e2 = b - a, c - a
+    nrm = np.cross(e1, e2)
+    area2 = np.linalg.norm(nrm, axis=1, keepdims=True)
+    ok = area2[:, 0] > 1e-12
+    nrm = nrm / np.where(area2 > 0, area2, 1.0)
+    w = rng.dirichlet([1, 1, 1], n)
+    p = a * w[:, :1] + b * w[:, 1:2] + c * w[:, 2:3]
+    th = rng.uniform(0, 2 * np.pi, (n, 1))
+    u1 = e1 / np.maximum(np.linalg.norm(e1, axis=1, keepdims=True), 1e-300)
+    u2 = np.cross(nrm, u1)
+    u = np.cos(th) * u1 + np.sin(th) * u2                      # unit vector in the triangle's plane
+    dist = rng.uniform(0.3, 12.0, (n, 1))
+    s = 10.0 ** rng.uniform(-1, 1, (n, 1))                     # the reference never normalises camera rays (engine.rs:207-211)
+    eps = 10.0 ** rng.uniform(np.log10(eps_lo), np.log10(eps_hi), (n, 1)) * rng.choice([-1.0, 1.0], (n, 1))
+    d = u * s + nrm * (eps * s)
+    o = p - u * dist + nrm * (-eps * dist)                     # meets the plane near p
+    z = rng.random(n) < 0.33                                   # a third of the rays exactly in the plane, up to rounding
+    d[z] = (u * s)[z]
+    o[z] = (p - u * dist)[z]
+    return o[ok], d[ok], tri[ok]
+
+
+def reference_determinant_rel(sd, tri_ids, d):
+    """|a| / (|e1| |e2| |d|) of ray.rs:64 for the given triangles and directions: how far the ray is from the triangle's
+    plane, in radians; rounding noise of `a` itself is ~1e-16 on this scale."""
+    v = np.asarray(sd.v, dtype=np.float64).reshape(-1, 3, 3)[tri_ids]
+    e1, e2 = v[:, 1] - v[:, 0], v[:, 2] - v[:, 0]
+    a = np.einsum("ij,ij->i", e1, np.cross(d, e2))
+    den = np.linalg.norm(e1, axis=1) * np.linalg.norm(e2, axis=1) * np.linalg.norm(d, axis=1)
+    return np.abs(a) / np.maximum(den, 1e-300)

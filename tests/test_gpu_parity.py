@@ -8,7 +8,7 @@ import os
 import numpy as np
 import pytest
 
-from conftest import random_scene, rgb_planes, tiny_scene
+from conftest import grazing_rays, random_scene, reference_determinant_rel, rgb_planes, tiny_scene
 
 pytestmark = pytest.mark.gpu
 
@@ -137,3 +137,57 @@ def test_rays_outside_the_f32_culling_range_bit_exact(rrt, scenes):
     assert np.array_equal(tuv[tri >= 0], otuv[otri >= 0])
     assert (tri >= 0).sum() > 1000
     rt.close()
+
+
+def test_grazing_rays_the_documented_exception_of_the_culling(rrt, scenes, monkeypatch):
+    # DESIGN.md §5.4 on the GPU: 10^6 adversarial rays built in (or within 1e-16 .. 1e-8 rad of) triangle planes of the
+    # teapot scene.  With the culling off every ray equals the oracle; with it on (the default) the few rays that
+    # differ all have a reference hit whose determinant is rounding noise (|a| < 1e-11 |e1||e2||d|).
+    from oracle.oracle import OracleScene
+    sd = scenes("model2")
+    rng = np.random.default_rng(7)
+    o, d, built_on = grazing_rays(sd, 1_000_000, rng)
+    otri, otuv = OracleScene(sd).trace(o, d)
+    rt = rrt.RayTracer(sd)
+    tri, tuv = rt.intersect_with_octant_with_max_t(o, d)
+    rt.close()
+    bad = np.nonzero(tri != otri)[0]
+    assert bad.size < 5e-4 * len(o), bad.size
+    hidden = bad[otri[bad] >= 0]
+    assert (reference_determinant_rel(sd, otri[hidden], d[hidden]) < 1e-11).all()
+    same = tri == otri
+    assert np.array_equal(tuv[same & (tri >= 0)], otuv[same & (tri >= 0)])
+    monkeypatch.setenv("RRT_CULL_THRESHOLD", "0")
+    monkeypatch.setenv("RRT_SEARCH_MODE", "0")
+    rt0 = rrt.RayTracer(sd)                      # every list scanned in full, no scene-wide hierarchy: the reference's scan
+    tri0, tuv0 = rt0.intersect_with_octant_with_max_t(o, d)
+    rt0.close()
+    assert np.array_equal(tri0, otri)
+    assert np.array_equal(tuv0[tri0 >= 0], otuv[otri >= 0])
+
+
+def test_ten_million_random_rays_through_the_searches(rrt, scenes):
+    # the searches of the scene-wide hierarchy (scene_clear / sparse_closest) on 10^7 rays of the
+    # kinds that stress their hand-over rules: camera-like rays from outside, rays from origins INSIDE the geometry
+    # (the origin-inside tie rule of ray.rs:49-53), origins exactly on octree planes, zero direction components —
+    # closest hit (t, u, v, id) bit for bit against the oracle, on the teapot scene and on a triangle soup
+    from oracle.oracle import OracleScene
+    from rrt_b200.synthetic import triangle_soup
+    for sd, centre, extent, n in ((scenes("model2"), np.array([0.0, 3.0, 0.0]), 9.0, 8_000_000),
+                                  (triangle_soup(40000, size=0.4), np.zeros(3), 18.0, 2_000_000)):
+        rng = np.random.default_rng(11)
+        o = rng.uniform(-extent, extent, (n, 3)) + centre
+        d = rng.normal(size=(n, 3))
+        cam = np.arange(n) % 3 == 0                                  # a third: the reference camera, engine.rs:207-211
+        o[cam] = np.array([0.0, 2.0, -10.0])
+        d[cam] = np.stack([rng.uniform(-0.5, 0.5, cam.sum()), rng.uniform(-0.5, 0.5, cam.sum()), np.ones(cam.sum())], 1)
+        o[5::23] = np.round(o[5::23] / 2.5) * 2.5                    # origins ON octree planes (k * 2.5 in the +-20 root box)
+        d[7::31, rng.integers(0, 3)] = 0.0
+        rt, osc = rrt.RayTracer(sd), OracleScene(sd)
+        tri, tuv = rt.intersect_with_octant_with_max_t(o, d)
+        otri, otuv = osc.trace(o, d)
+        assert np.array_equal(tri, otri)
+        assert np.array_equal(tuv[tri >= 0], otuv[otri >= 0])
+        assert (tri >= 0).mean() > 0.2
+        rt.close()
+        osc.close()
