@@ -203,6 +203,23 @@ int rrt_render_frames(rrt_scene* scene, const rrt_render_params* params, int32_t
 int rrt_render_device(rrt_scene* scene, const rrt_render_params* params, const rrt_shard* shard,
                       uint32_t* d_fb, int32_t* d_hit_ids, void* cuda_stream);
 
+/* Allocation-free variant of rrt_render_device.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same arguments, same result in d_fb (and d_hit_ids, may be NULL), enqueued on
+ * `cuda_stream`, does not synchronise — but it calls no cudaMalloc / cudaFree and no allocating library routine:
+ * the kernel's scratch (per-pixel accumulators + queue head) is a static device array inside the library, 8 MiB held
+ * by every GPU that loads the library until the process exits.  Limits and rules:
+ *   - the shard may hold at most RRT_NOALLOC_MAX_PIXELS pixels (rows owned x width; 1920x1080 fits), larger calls
+ *     return RRT_ERR_INVALID with a message that names both numbers;
+ *   - every call on a GPU shares the one array (it is cleared on the stream before use): calls that OVERLAP on the
+ *     GPU — two streams, two threads, two scene handles — race; issue them one after another;
+ *   - the dispatch-order hint (rrt_scene_order_hint) is not used: its arrays are allocated on demand;
+ *   - the first call on a device resolves the array's address and the kernel's occupancy (no allocation, but make one
+ *     warm-up call before capturing a graph). */
+#define RRT_NOALLOC_MAX_PIXELS (1u << 21)
+int rrt_render_device_noalloc(rrt_scene* scene, const rrt_render_params* params, const rrt_shard* shard,
+                              uint32_t* d_fb, int32_t* d_hit_ids, void* cuda_stream);
+
 /* Fused render + gather: the shard's rows are stored straight into a FULL frame (row r of the frame at
  * d_frame[r*width ...], reference layout), which may live on ANOTHER GPU: a pointer obtained from
  * rrt_ipc_open_handle() on a frame a peer process allocated with rrt_frame_alloc().  Every pixel is

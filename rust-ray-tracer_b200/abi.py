@@ -72,12 +72,14 @@ class Counters(C.Structure):
         return {n: int(getattr(self, n)) for n, _ in self._fields_}
 
 
+RRT_NOALLOC_MAX_PIXELS = 1 << 21   # include/rrt.h
+
 # every symbol include/rrt.h declares (tests check the .so exports all of them)
 SYMBOLS = [
     "rrt_abi_version", "rrt_last_error", "rrt_device_count", "rrt_render_params_default",
     "rrt_scene_create", "rrt_scene_destroy", "rrt_scene_get_stats", "rrt_scene_order_hint",
     "rrt_scene_search_mode", "rrt_scene_search_state",
-    "rrt_render", "rrt_render_frames", "rrt_render_device", "rrt_shard_rows", "rrt_deinterleave_device",
+    "rrt_render", "rrt_render_frames", "rrt_render_device", "rrt_render_device_noalloc", "rrt_shard_rows", "rrt_deinterleave_device",
     "rrt_render_device_into_frame", "rrt_frame_alloc", "rrt_frame_free", "rrt_ipc_get_handle", "rrt_ipc_open_handle",
     "rrt_ipc_close_handle", "rrt_copy_frame_to_host",
     "rrt_host_frame_create", "rrt_host_frame_open", "rrt_host_frame_pixels", "rrt_host_frame_geometry",
@@ -119,6 +121,7 @@ def lib():
     L.rrt_render.argtypes = [vp, C.POINTER(RenderParams), vp, vp, C.POINTER(C.c_float)]
     L.rrt_render_frames.argtypes = [vp, C.POINTER(RenderParams), C.c_int32, C.POINTER(vp), C.POINTER(C.c_float)]
     L.rrt_render_device.argtypes = [vp, C.POINTER(RenderParams), C.POINTER(Shard), vp, vp, vp]
+    L.rrt_render_device_noalloc.argtypes = [vp, C.POINTER(RenderParams), C.POINTER(Shard), vp, vp, vp]
     L.rrt_render_device_into_frame.argtypes = [vp, C.POINTER(RenderParams), C.POINTER(Shard), vp, vp]
     L.rrt_frame_alloc.argtypes = [C.c_int, i32, i32, C.POINTER(vp)]
     L.rrt_frame_free.argtypes = [C.c_int, vp]

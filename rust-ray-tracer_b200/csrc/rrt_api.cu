@@ -17,6 +17,8 @@
 
 using namespace rrt;
 
+static_assert(RRT_NOALLOC_MAX_PIXELS == kNoAllocMaxPixels, "include/rrt.h and rrt_render.h state one limit");
+
 namespace {
 
 thread_local std::string g_err = "";
@@ -396,6 +398,25 @@ int rrt_render_device(rrt_scene* s, const rrt_render_params* p, const rrt_shard*
     CU(cudaSetDevice(s->device));
     if ((rc = ensure(&s->d_scratch, &s->scratch_cap, render_scratch_words(P.n_rows_local, P.W)))) return rc;
     CU(render_frame(s, P, d_fb, d_hit_ids, nullptr, (cudaStream_t)cuda_stream));
+    return RRT_OK;
+}
+
+// Allocation-free rrt_render_device (no counterpart in the reference):
+// calls no cudaMalloc / cudaFree and no allocating library routine — the kernel's scratch is a static device array
+// of rrt_render.cu, so the shard may hold at most RRT_NOALLOC_MAX_PIXELS pixels.
+int rrt_render_device_noalloc(rrt_scene* s, const rrt_render_params* p, const rrt_shard* shard, uint32_t* d_fb,
+                              int32_t* d_hit_ids, void* cuda_stream) {
+    if (!s || !d_fb) return fail(RRT_ERR_INVALID, "null argument");
+    DevParams P;
+    int rc = make_params(s, p, shard, &P);
+    if (rc) return rc;
+    const unsigned long long npix = (unsigned long long)P.n_rows_local * (unsigned long long)P.W;
+    if (npix > (unsigned long long)RRT_NOALLOC_MAX_PIXELS)
+        return fail(RRT_ERR_INVALID, "rrt_render_device_noalloc: " + std::to_string(npix) + " pixels exceed the static scratch of " +
+                                         std::to_string((unsigned long long)RRT_NOALLOC_MAX_PIXELS) +
+                                         " pixels (RRT_NOALLOC_MAX_PIXELS); render it in shards or use rrt_render_device");
+    CU(cudaSetDevice(s->device));
+    CU(launch_render_noalloc(s->dev, P, d_fb, d_hit_ids, (cudaStream_t)cuda_stream));
     return RRT_OK;
 }
 

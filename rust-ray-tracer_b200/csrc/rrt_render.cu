@@ -7,6 +7,14 @@
 
 #include <mutex>
 
+// Scratch of the allocation-free render call (rrt_render_device_noalloc, no
+// counterpart in the reference): the per-pixel accumulators + the sample-queue head that launch_render otherwise gets
+// from a cudaMalloc'ed buffer of the scene handle.  File scope, one copy per GPU that loads this library, held until
+// the process exits: kNoAllocMaxPixels * 4 + 16 bytes = 8 MiB + 16 B.  In HOST code this name is only a stand-in for
+// the device array (not a device address): the launcher below resolves it with cudaGetSymbolAddress once per device.
+// The limit itself is rrt::kNoAllocMaxPixels in rrt_render.h (RRT_NOALLOC_MAX_PIXELS in include/rrt.h).
+static __device__ __align__(256) uint32_t g_noalloc_scratch[((size_t)1 << 21) + 4];
+
 namespace rrt {
 
 namespace {
@@ -435,6 +443,56 @@ extern "C" int rrt_debug_timeline(unsigned long long* out, int reset) {
 
 
 size_t render_scratch_words(int n_rows_local, int W) { return (((size_t)n_rows_local * W + 1) & ~(size_t)1) + 2; }
+
+static_assert(sizeof(g_noalloc_scratch) / sizeof(uint32_t) == (size_t)kNoAllocMaxPixels + 4, "static scratch size");
+
+// Device address of g_noalloc_scratch on the CURRENT device, resolved once per device (set-up of the allocation-free
+// call): cudaGetSymbolAddress with that device current, return code checked, result cached under a mutex.
+static cudaError_t noalloc_scratch_ptr(uint32_t** out) {
+    constexpr int kMaxDev = 64;
+    static std::mutex mu;
+    static uint32_t* ptr[kMaxDev];   // zero-initialised: nullptr = not resolved yet
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= kMaxDev) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ptr[dev]) {
+        void* p = nullptr;
+        if ((e = cudaGetSymbolAddress(&p, g_noalloc_scratch)) != cudaSuccess) return e;
+        if (!p) return cudaErrorInvalidSymbol;
+        ptr[dev] = static_cast<uint32_t*>(p);
+    }
+    *out = ptr[dev];
+    return cudaSuccess;
+}
+
+// launch_render without any allocation: the scratch is the static device array above, the dispatch-order hint (whose
+// arrays and cub temporary are allocated on demand) is left out, so the kernel is render_kernel<false, false>.  The
+// array keeps the previous call's contents: the part this call uses is cleared first (cudaMemsetAsync on `stream`).
+// Every call on a device shares the array — calls that overlap on the GPU race.
+cudaError_t launch_render_noalloc(const DevScene& sc, const DevParams& P, uint32_t* d_fb, int32_t* d_hit, cudaStream_t stream) {
+    if ((size_t)P.n_rows_local * (size_t)P.W > (size_t)kNoAllocMaxPixels) return cudaErrorInvalidValue;
+    const int tiles_x = (P.W + kTileW - 1) / kTileW, tiles_y = (P.n_rows_local + kTileH - 1) / kTileH;
+    const unsigned long long total = (unsigned long long)tiles_x * tiles_y * (kTileW * kTileH * 4);
+    if (total == 0) return cudaSuccess;
+    uint32_t* scratch = nullptr;
+    cudaError_t e = noalloc_scratch_ptr(&scratch);
+    if (e != cudaSuccess) return e;
+    const size_t npix = (size_t)P.n_rows_local * P.W;
+    const size_t head = (npix + 1) & ~(size_t)1;  // 8-byte aligned
+    if ((e = cudaMemsetAsync(scratch, 0, (head + 2) * sizeof(uint32_t), stream)) != cudaSuccess) return e;
+    int n_sm = 0, per_sm = 0;
+    if ((e = render_occupancy(0, &n_sm, &per_sm)) != cudaSuccess) return e;
+    const unsigned long long want = (total + kBlock - 1) / kBlock;
+    const unsigned long long resident = (unsigned long long)n_sm * per_sm;
+    const unsigned grid = (unsigned)(want < resident ? want : resident);
+    unsigned long long* next = reinterpret_cast<unsigned long long*>(scratch + head);
+    render_kernel<false, false><<<grid, kBlock, 0, stream>>>(sc, P, d_fb, d_hit, scratch, next, nullptr, tiles_x, total, nullptr, nullptr);
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    if (P.search_mode == 1) search_switch_kernel<<<1, 1, 0, stream>>>(P.fstat);
+    return cudaGetLastError();
+}
 
 cudaError_t launch_trace(const DevScene& sc, uint64_t n, const double* o, const double* d, const double* max_t,
                          int32_t* out_tri, double* out_tuv, bool searches, cudaStream_t stream) {

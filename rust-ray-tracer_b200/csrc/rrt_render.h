@@ -35,6 +35,10 @@ struct RenderSchedule {
 cudaError_t launch_render(const DevScene& sc, const DevParams& P, uint32_t* d_fb, int32_t* d_hit, uint32_t* d_scratch,
                           DevCounters* d_counters, cudaStream_t stream, RenderSchedule* sch = nullptr);
 size_t render_scratch_words(int n_rows_local, int W);
+// Allocation-free variant (rrt_render_device_noalloc): scratch in a static device array of rrt_render.cu, at most
+// kNoAllocMaxPixels pixels per call (cudaErrorInvalidValue beyond), no dispatch-order hint.
+constexpr uint32_t kNoAllocMaxPixels = 1u << 21;   // == RRT_NOALLOC_MAX_PIXELS (include/rrt.h): 2 Mi pixels, 8 MiB of scratch
+cudaError_t launch_render_noalloc(const DevScene& sc, const DevParams& P, uint32_t* d_fb, int32_t* d_hit, cudaStream_t stream);
 // searches: let rays be answered by the scene-wide hierarchy where that is exact (rrt_trace.cuh); false = walk only
 cudaError_t launch_trace(const DevScene& sc, uint64_t n, const double* o, const double* d, const double* max_t,
                          int32_t* out_tri, double* out_tuv, bool searches, cudaStream_t stream);
