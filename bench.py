@@ -176,6 +176,36 @@ def kernel_id():
         return None
 
 
+def roofline_block(prof, w, kern_ms, have_prof, kid, fp64_peak, hbm_peak, hbm_src, clocks, n_sm):
+    """The `roofline` object of the JSON line.  Every count comes from the committed ncu capture of workload `w`
+    (profiles/traffic.json, written by tools/ncu_digest.py); every time and peak is measured in this run.  Without a
+    capture of this workload (or at N > 1, where one launch covers a shard) the fractions are null, never a guess."""
+    sec = kern_ms * 1e-3
+    warp_inst, lane_inst, traffic = prof.get(w + "_warp_inst"), prof.get(w + "_fp64_lane_inst"), prof.get(w)
+    mhz = (clocks or {}).get("sm_mhz") or (clocks or {}).get("sm_max_mhz") or 1965.0
+    issue_peak = n_sm * 4 * mhz * 1e6 / 1e9                      # G warp-instructions / s
+    a_issue = warp_inst / sec / 1e9 if have_prof and warp_inst else None
+    a_fp64 = lane_inst / sec / 1e12 if have_prof and lane_inst else None
+    a_dram = traffic / sec / 1e9 if have_prof and traffic else None
+    lanes = prof.get(w + "_avg_active_lanes")
+    return {
+        "bound": "issue", "kernel": "render_kernel", "achieved": a_issue, "peak": issue_peak,
+        "unit": "G warp-instructions/s (SMs x 4 schedulers x SM clock)", "frac": (a_issue / issue_peak) if a_issue else None,
+        "traffic": traffic, "kernel_ms": kern_ms, "warp_inst_per_launch": warp_inst, "sm_mhz": mhz, "n_sm": n_sm,
+        "avg_active_lanes": lanes,
+        "lane_frac": (a_issue / issue_peak * lanes / 32.0) if (a_issue and lanes) else None,
+        "issue_active_pct_ncu": prof.get(w + "_issue_active_pct"),
+        "fp64": {"achieved": a_fp64, "peak": fp64_peak, "frac": (a_fp64 / fp64_peak) if a_fp64 else None,
+                 "unit": "T FP64 lane-instructions/s (DADD/DMUL/DFMA/DSETP executed; peak = DMUL+DADD without FMA, measured live)",
+                 "lane_inst_per_launch": lane_inst, "pipe_active_pct_ncu": prof.get(w + "_fp64_pipe_active_pct")},
+        "dram": {"achieved": a_dram, "peak": hbm_peak, "frac": (a_dram / hbm_peak) if a_dram else None, "unit": "GB/s",
+                 "peak_source": hbm_src, "note": "dram__bytes_read+write of one launch; mostly local-memory write-back, not the limiter"},
+        "profile": {"source": prof.get(w + "_source"), "kernel_id": prof.get(w + "_kernel_id"),
+                    "kernel_ms_under_ncu": prof.get(w + "_kernel_ms_under_ncu"),
+                    "matches_this_build": bool(kid and prof.get(w + "_kernel_id") == kid)},
+    }
+
+
 def run_gpu(args):
     import numpy as np
     import torch
@@ -383,10 +413,7 @@ def run_gpu(args):
         w = args.workload
         kid = kernel_id()
         have_prof = world == 1 and (w + "_fp64_lane_inst") in prof
-        lane_inst = prof.get(w + "_fp64_lane_inst")
-        traffic = prof.get(w)
         order_hint = os.environ.get("RRT_ORDER_HINT", "1") != "0"
-        a_lane = lane_inst / (kern_ms * 1e-3) / 1e12 if have_prof else None
         line = {
             "metric": "Mrays/s (primary rays, 4 per pixel)", "value": value, "unit": "Mrays/s", "n_gpus": world,
             "steps": K, "warmup": Wm, "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "strong",
@@ -419,23 +446,13 @@ def run_gpu(args):
             # dispatch-order hint; the cub radix-sort kernels behind them are library code and not counted)
             "gpu_launches": K * ((4 if order_hint else 2) + (1 if world > 1 and sr.mode == "nccl" else 0)),
             "parity": parity,
-            # The kernel is bound by the FP64 vector pipe and instruction issue, not by HBM (the scene is L2-resident):
-            # achieved = FP64-pipe lane instructions the kernel EXECUTES per launch (ncu opcode counts of the committed
-            # capture of this workload, profiles/traffic.json) / live kernel time; peak = DMUL+DADD without FMA measured live.
-            "roofline": {"bound": "fp64", "kernel": "render_kernel", "achieved": a_lane, "peak": fp64.value,
-                         "unit": "T FP64 lane-instructions/s (DADD/DMUL/DFMA/DSETP executed, one per active lane)",
-                         "frac": (a_lane / fp64.value) if have_prof else None,
-                         "traffic": traffic, "kernel_ms": kern_ms,
-                         "fp64_lane_inst_per_launch": lane_inst,
-                         "issue_active_pct": prof.get(w + "_issue_active_pct"),
-                         "fp64_pipe_active_pct": prof.get(w + "_fp64_pipe_active_pct"),
-                         "avg_active_lanes": prof.get(w + "_avg_active_lanes"),
-                         "dram_gbs": (traffic / (kern_ms * 1e-3) / 1e9) if (have_prof and traffic) else None,
-                         "dram_frac_of_measured_hbm": (traffic / (kern_ms * 1e-3) / 1e9 / hbm_peak) if (have_prof and traffic) else None,
-                         "hbm_peak_gbs": hbm_peak, "hbm_peak_source": hbm_src,
-                         "profile": {"source": prof.get(w + "_source"), "kernel_id": prof.get(w + "_kernel_id"),
-                                     "matches_this_build": bool(kid and prof.get(w + "_kernel_id") == kid)},
-                         "note": "N>1 and workloads without a committed capture: achieved/frac are null (never a guess)"},
+            # Neither HBM nor tensor cores bound this kernel (scene L2-resident, no contraction): ncu names INSTRUCTION ISSUE
+            # as the limiter, so that is the roofline reported.  achieved = warp instructions the kernel executes per launch
+            # (smsp__inst_executed.sum of the committed ncu capture of this workload, profiles/traffic.json) / live kernel
+            # time; peak = SMs x 4 schedulers x 1 instruction per cycle x the SM clock sampled during the timed region.
+            # The FP64 pipe (DMUL+DADD peak without FMA measured live) and DRAM (measured copy peak) stand beside it.
+            "roofline": roofline_block(prof, w, kern_ms, have_prof, kid, fp64.value, hbm_peak, hbm_src, clocks,
+                                       torch.cuda.get_device_properties(dev).multi_processor_count),
             # what the REFERENCE executes per primary ray (SURVEY 8d formula on the oracle's counters) against what this
             # kernel executes: an algorithmic speed-up, NOT a roofline fraction
             "algorithmic_speedup": {"reference_flops_per_ray": flops_ray, "reference_bytes_per_ray": bytes_ray,

@@ -265,6 +265,16 @@ void rrt_host_frame_close(rrt_host_frame* f);                /* the creator also
 int rrt_render_to_host_frame(rrt_scene* scene, const rrt_render_params* params, const rrt_shard* shard,
                              uint32_t* host_frame, void* cuda_stream);
 
+/* The copy half of rrt_render_to_host_frame on its own: d_rows = the shard's rows as rrt_render_device wrote them
+ * (compact, device memory of `device`), enqueued on `cuda_stream`.  Lets a caller launch the render, THEN wait for
+ * "the previous frame has been read" (rrt_host_frame_barrier), then enqueue the copy: the wait hides behind the kernel. */
+int rrt_copy_shard_to_host_frame(int device, const uint32_t* d_rows, int32_t width, int32_t height, const rrt_shard* shard,
+                                 uint32_t* host_frame, void* cuda_stream);
+
+/* Waits for everything enqueued on `cuda_stream` (NULL = default stream) of the scene's device: the asynchronous calls
+ * above for a host that does not link the CUDA runtime itself (the Rust crate; tests/native/multi_rank_driver.cpp). */
+int rrt_synchronize(rrt_scene* scene, void* cuda_stream);
+
 /* Number of buffer rows shard `shard_index` owns for a frame of `height` rows (row 0 included). */
 int rrt_shard_rows(int32_t height, const rrt_shard* shard);
 

@@ -84,7 +84,7 @@ SYMBOLS = [
     "rrt_ipc_close_handle", "rrt_copy_frame_to_host",
     "rrt_host_frame_create", "rrt_host_frame_open", "rrt_host_frame_pixels", "rrt_host_frame_geometry",
     "rrt_host_frame_pin", "rrt_host_frame_barrier", "rrt_host_frame_publish_handle", "rrt_host_frame_fetch_handle",
-    "rrt_host_frame_close", "rrt_render_to_host_frame",
+    "rrt_host_frame_close", "rrt_render_to_host_frame", "rrt_copy_shard_to_host_frame", "rrt_synchronize",
     "rrt_trace_rays", "rrt_ray_colours", "rrt_render_counters",
     "rrt_octree_build", "rrt_octree_destroy", "rrt_octree_node_count", "rrt_octree_node", "rrt_octree_node_list",
     "rrt_octree_flatten_stats", "rrt_octree_digest",
@@ -141,6 +141,8 @@ def lib():
     L.rrt_host_frame_close.argtypes = [vp]
     L.rrt_host_frame_close.restype = None
     L.rrt_render_to_host_frame.argtypes = [vp, C.POINTER(RenderParams), C.POINTER(Shard), vp, vp]
+    L.rrt_synchronize.argtypes = [vp, vp]
+    L.rrt_copy_shard_to_host_frame.argtypes = [C.c_int, vp, i32, i32, C.POINTER(Shard), vp, vp]
     L.rrt_shard_rows.argtypes = [i32, C.POINTER(Shard)]
     L.rrt_deinterleave_device.argtypes = [C.c_int, vp, i32, i32, i32, i32, i32, vp, vp]
     L.rrt_trace_rays.argtypes = [vp, u64, vp, vp, vp, vp, vp]

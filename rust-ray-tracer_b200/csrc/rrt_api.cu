@@ -478,9 +478,30 @@ int rrt_copy_frame_to_host(int device, const uint32_t* d_frame, int32_t width, i
     return RRT_OK;
 }
 
-// The shard's rows, rendered compactly into the handle's device buffer, leave for their places in a FULL frame in
-// host memory: tile row j of the frame (tile_rows scan-lines) is the shard's j / n_shards-th group, so one pitched
-// copy moves every whole group and a second one the ragged last group (only the frame's last tile row can be short).
+// A shard's compact rows leave for their places in a FULL frame in host memory: tile row j of the frame (tile_rows
+// scan-lines) is the shard's j / n_shards-th group, so one pitched copy moves every whole group and a second one the
+// ragged last group (only the frame's last tile row can be short).
+int rrt_copy_shard_to_host_frame(int device, const uint32_t* d_rows, int32_t width, int32_t height, const rrt_shard* shard,
+                                 uint32_t* host_frame, void* cuda_stream) {
+    if (!d_rows || !host_frame || width <= 0 || height <= 0) return fail(RRT_ERR_INVALID, "bad argument");
+    rrt_shard one{1, 1, 0};
+    const rrt_shard* sh = shard ? shard : &one;
+    if (sh->tile_rows < 1 || sh->n_shards < 1 || sh->shard_index < 0 || sh->shard_index >= sh->n_shards)
+        return fail(RRT_ERR_INVALID, "bad shard");
+    CU(cudaSetDevice(device));
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    const int rows = rrt_shard_rows(height, sh);
+    const size_t row_bytes = (size_t)width * sizeof(uint32_t), group = row_bytes * sh->tile_rows;
+    const int n_full = rows / sh->tile_rows, rest = rows % sh->tile_rows;
+    uint32_t* dst0 = host_frame + (size_t)sh->shard_index * sh->tile_rows * width;
+    if (n_full > 0)
+        CU(cudaMemcpy2DAsync(dst0, group * sh->n_shards, d_rows, group, group, (size_t)n_full, cudaMemcpyDeviceToHost, st));
+    if (rest > 0)
+        CU(cudaMemcpyAsync(dst0 + (size_t)n_full * sh->n_shards * sh->tile_rows * width, d_rows + (size_t)n_full * sh->tile_rows * width,
+                           row_bytes * rest, cudaMemcpyDeviceToHost, st));
+    return RRT_OK;
+}
+
 int rrt_render_to_host_frame(rrt_scene* s, const rrt_render_params* p, const rrt_shard* shard, uint32_t* host_frame,
                              void* cuda_stream) {
     if (!s || !host_frame) return fail(RRT_ERR_INVALID, "null argument");
@@ -493,14 +514,13 @@ int rrt_render_to_host_frame(rrt_scene* s, const rrt_render_params* p, const rrt
     if ((rc = ensure(&s->d_fb, &s->fb_cap, n))) return rc;
     if ((rc = ensure(&s->d_scratch, &s->scratch_cap, render_scratch_words(P.n_rows_local, P.W)))) return rc;
     CU(render_frame(s, P, s->d_fb, nullptr, nullptr, st));
-    const size_t row_bytes = (size_t)P.W * sizeof(uint32_t), group = row_bytes * P.tile_rows;
-    const int n_full = P.n_rows_local / P.tile_rows, rest = P.n_rows_local % P.tile_rows;
-    uint32_t* dst0 = host_frame + (size_t)P.shard_index * P.tile_rows * P.W;
-    if (n_full > 0)
-        CU(cudaMemcpy2DAsync(dst0, group * P.n_shards, s->d_fb, group, group, (size_t)n_full, cudaMemcpyDeviceToHost, st));
-    if (rest > 0)
-        CU(cudaMemcpyAsync(dst0 + (size_t)n_full * P.n_shards * P.tile_rows * P.W, s->d_fb + (size_t)n_full * P.tile_rows * P.W,
-                           row_bytes * rest, cudaMemcpyDeviceToHost, st));
+    return rrt_copy_shard_to_host_frame(s->device, s->d_fb, P.W, P.H, shard, host_frame, cuda_stream);
+}
+
+int rrt_synchronize(rrt_scene* s, void* cuda_stream) {
+    if (!s) return fail(RRT_ERR_INVALID, "null scene");
+    CU(cudaSetDevice(s->device));
+    CU(cudaStreamSynchronize((cudaStream_t)cuda_stream));
     return RRT_OK;
 }
 

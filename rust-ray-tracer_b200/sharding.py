@@ -91,8 +91,8 @@ class ShardedRenderer:
         before calling render() again.
     assemble="host": the frame is wanted in HOST memory (the reference's Canvas.buffer, engine.rs:123-128): every
         rank renders compactly and copies ITS rows over its own PCIe link into one page-locked shared-memory
-        frame (HostFrame); assemble() = stream sync + a process-shared barrier ("frame complete"), the next
-        render() begins with a second barrier ("rank 0 is done reading").  No device-side exchange at all.
+        frame (HostFrame); assemble() = a barrier ("rank 0 is done reading the previous frame", waited for while the
+        kernel runs), the copy, a stream sync and a second barrier ("frame complete").  No device-side exchange at all.
     """
 
     def __init__(self, ray_tracer, width, height, rank, world, tile_rows=DEFAULT_TILE_ROWS, group=None,
@@ -131,6 +131,8 @@ class ShardedRenderer:
         if self.rank != 0:
             self._host = HostFrame(box[0], self.W, self.H, self.world, create=False, device=self.rt.device)
         self.frame = self._host.pixels        # numpy (H, W) u32 view of the shared canvas
+        import torch
+        self._rows = torch.zeros((max(self.n_local, 1), self.W), dtype=torch.int32, device=self.device)   # this rank's compact rows
 
     def _setup_peer_frames(self):
         import torch
@@ -188,11 +190,9 @@ class ShardedRenderer:
                                                              C.c_void_p(self._dest[self._cur]), C.c_void_p(s.cuda_stream)))
             return
         if self.mode == "host":
-            if self._outstanding and self.world > 1:
-                self._host.barrier()          # rank 0 has finished reading the previous frame
-            self._outstanding = False
-            abi.check(abi.lib().rrt_render_to_host_frame(self.rt.handle, C.byref(params), C.byref(self.shard),
-                                                         C.c_void_p(self._host.ptr), C.c_void_p(s.cuda_stream)))
+            # render first; "rank 0 has finished reading the previous frame" is only needed before the COPY (assemble)
+            abi.check(abi.lib().rrt_render_device(self.rt.handle, C.byref(params), C.byref(self.shard),
+                                                  self._rows.data_ptr(), None, C.c_void_p(s.cuda_stream)))
             return
         out = self.local if self.world > 1 else self.frame
         abi.check(abi.lib().rrt_render_device(self.rt.handle, C.byref(params), C.byref(self.shard),
@@ -206,9 +206,14 @@ class ShardedRenderer:
         import torch.distributed as dist
         s = stream or torch.cuda.current_stream(self.device)
         if self.mode == "host":
+            if self._outstanding and self.world > 1:
+                self._host.barrier()          # rank 0 has finished reading the previous frame (waited for behind the kernel)
+            abi.check(abi.lib().rrt_copy_shard_to_host_frame(self.rt.device, self._rows.data_ptr(), self.W, self.H,
+                                                             C.byref(self.shard), C.c_void_p(self._host.ptr),
+                                                             C.c_void_p(s.cuda_stream)))
             s.synchronize()
             if self.world > 1:
-                self._host.barrier()
+                self._host.barrier()          # every rank's rows have landed: the frame is complete
             self._outstanding = True
             return self.frame
         if self.world == 1:
