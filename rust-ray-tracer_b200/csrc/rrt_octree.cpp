@@ -697,7 +697,7 @@ void flatten(const HostOctree& t, const double* v, uint32_t cull_threshold, uint
     }
     // The way UP from a record: its node, a node's parent and which reference child of it the node is; and whether
     // every stored triangle lies inside the box of the node that stores it (false when a triangle pokes out of the
-    // root box, utils.rs:145 / octree.rs:71-73) with a root box of sane size — sparse_closest's precondition (a).
+    // root box, utils.rs:145 / octree.rs:71-73) with a root box of sane size — precondition (a) of scene_search for camera rays.
     {
         bool inside = true;
         for (size_t d = 0; d < out->nodes.size(); ++d) {
@@ -723,7 +723,7 @@ void flatten(const HostOctree& t, const double* v, uint32_t cull_threshold, uint
         out->sparse_ok = inside && rmax <= 1e4 * out->scale;
     }
     // ONE more culling hierarchy over ALL records of the scene, every leaf a single record, for the searches that go
-    // round the octree walk (rrt_trace.cuh: scene_clear, sparse_closest) — which record belongs to which octree node
+    // round the octree walk (rrt_trace.cuh: scene_search) — which record belongs to which octree node
     // does not matter to their questions.  n - 1 inner nodes, built as OpenMP tasks on disjoint ranges.
     if (global_hierarchy && tight && out->scale < INFINITY && out->tris.size() > 1 && out->tris.size() < (1u << 28)) {
         const size_t nr = out->tris.size();

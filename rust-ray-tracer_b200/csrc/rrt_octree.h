@@ -129,7 +129,7 @@ struct FlatScene {
     double scale = 1.0;        // S = max(1, largest |coordinate| of a stored triangle): culling pad / eligibility unit
     uint32_t global_root = 0;  // 1 + DevCull index of the root of the scene-wide hierarchy over ALL records (0 = none)
     bool sparse_ok = false;    // every stored triangle lies inside its node's box and the root box is at most 1e4 S
-                               // across: precondition (a) of sparse_closest (rrt_trace.cuh)
+                               // across: precondition (a) of scene_search for camera rays (rrt_trace.cuh)
 };
 
 // Flatten: renumber kept nodes breadth-first (siblings consecutive), concatenate node lists.
@@ -138,7 +138,7 @@ struct FlatScene {
 // 0 = culling off: long lists still go through the same hierarchy code, but with infinite boxes, so
 // every record of the list is tested (the exact linear scan of the reference, in another order).
 // global_hierarchy: also build the scene-wide hierarchy (one more DevCull per record) for the searches that go round
-// the octree walk (rrt_trace.cuh: scene_clear, sparse_closest).
+// the octree walk (rrt_trace.cuh: scene_search).
 void flatten(const HostOctree& t, const double* v, uint32_t cull_threshold, uint32_t cull_leaf, FlatScene* out,
              bool global_hierarchy = true);
 

@@ -1,5 +1,5 @@
-// rrt_trace.cuh — octree traversal (ray.rs:96-168): the exact iterative short-stack walk, and two searches of ONE
-// scene-wide culling hierarchy that answer most rays without the walk where that is provably the walk's answer.
+// rrt_trace.cuh — octree traversal (ray.rs:96-168): the exact iterative short-stack walk, and the search of ONE
+// scene-wide culling hierarchy that answers most rays without the walk where that is provably the walk's answer.
 //
 // Why the iterative walk equals the reference recursion:
 // a node that accepts ANY own triangle returns Some, so every ancestor's child loop `break`s once that
@@ -183,17 +183,9 @@ __device__ __forceinline__ bool test_record(const V3& o, const V3& d, const DevT
 // ---------------------------------------------------------------- the exact walk
 // Ray::intersect_with_octant_with_max_t(octree, 0, max_t).  any_hit: the caller only needs Some/None
 // (shadow rays, raytracer.rs:181-187) — `best` only ever improves, so the first update decides.
-#ifndef RRT_WALK_INLINE
-#define RRT_WALK_INLINE 1
-#endif
 template <bool COUNT>
-#if RRT_WALK_INLINE
 __device__ __forceinline__ void walk(const DevScene& sc, const V3& o, const V3& d, const double max_t, const bool any_hit,
                                      Hit& best, TraceCount& tc) {
-#else
-static __device__ __noinline__ void walk(const DevScene sc, const V3 o, const V3 d, const double max_t, const bool any_hit,
-                                         Hit& best, TraceCount& tc) {
-#endif
     best.id = kNone;
     best.rec = 0;
     best.t = max_t;
@@ -236,9 +228,10 @@ static __device__ __noinline__ void walk(const DevScene sc, const V3 o, const V3
             uint32_t cur = __ldg(&n->cull_root);
             int csp = 0;
             bool live = true;
+            // rounds of "while inner node / while leaf": a lane that reaches a leaf waits for the others of its warp, so
+            // the exact tests below run with more lanes than one test per hierarchy step would (profiles/r02_experiments.md)
             while (live) {
-                const bool was_leaf = (cur & kLeafBit) != 0u;
-                if (!was_leaf) {
+                while (live && !(cur & kLeafBit)) {
                     const DevCull* __restrict__ c = sc.cull + cur;
                     if (COUNT) tc.cull += 2;
                     const float4* bp = reinterpret_cast<const float4*>(c);
@@ -259,7 +252,7 @@ static __device__ __noinline__ void walk(const DevScene sc, const V3 o, const V3
                         live = false;
                     }
                 }
-                if (was_leaf) {
+                while (live && (cur & kLeafBit)) {
                     const uint32_t first = cur & 0x0FFFFFFFu;
                     const uint32_t cnt = ((cur >> 28) & 7u) + 1u;
                     bool upd = false;
@@ -268,9 +261,9 @@ static __device__ __noinline__ void walk(const DevScene sc, const V3 o, const V3
                         if (COUNT) tc.mt++;
                         upd |= test_record(o, d, sc.tris, first + i, nb);
                     }
-                    if (any_hit && nb.id != kNone && nb.t < best.t) break;  // best will improve => Some
                     if (upd) limit = __double2float_ru(nb.t);
-                    if (csp != 0) cur = cstk[--csp];
+                    if (any_hit && nb.id != kNone && nb.t < best.t) live = false;  // best will improve => Some
+                    else if (csp != 0) cur = cstk[--csp];
                     else live = false;
                 }
             }
@@ -374,14 +367,14 @@ static __device__ __noinline__ void walk(const DevScene sc, const V3 o, const V3
     }
 }
 
-// ---------------------------------------------------------------- searches of the scene-wide hierarchy
+// ---------------------------------------------------------------- search of the scene-wide hierarchy
 // flatten builds ONE more culling hierarchy of the usual kind over ALL records of the scene (DevScene::global_root,
 // every leaf a single record): which octree node owns a record does not matter to the two questions below, and a
 // binary SAH hierarchy answers them in ~25 f32 box-pair steps where the walk visits ~10 octree nodes at ~300
-// instructions each.  Both are separate functions (not inlined into the walk): each gets its own register
-// allocation and the walk's code stays small (measurements: profiles/r02_experiments.md).
+// instructions each.  ONE function answers both (not inlined into the walk: its own register allocation, the walk's
+// code stays small, and a single copy of the loop in the instruction cache; measurements: profiles/r02_experiments.md).
 
-// What the searches read of the scene, handed over BY VALUE: taking the address of the kernel's DevScene parameter for a
+// What the search reads of the scene, handed over BY VALUE: taking the address of the kernel's DevScene parameter for a
 // non-inlined callee would turn every access to it, in the walk too, from a constant-bank operand into a generic load.
 struct SearchScene {
     const DevNode* nodes;
@@ -394,46 +387,14 @@ __device__ __forceinline__ SearchScene search_scene(const DevScene& sc) {
     return SearchScene{sc.nodes, sc.tris, sc.cull, sc.cull_o_max, sc.global_root, sc.sparse_ok, sc.planes_safe, 0u};
 }
 
-// (1) Shadow queries (triangle_exists_between_points, raytracer.rs:164-188).  The walk's result is the minimum-t own
-// hit over the nodes it visits, every one of them a record the exact test ACCEPTS with t < max_t at the root
-// (ray.rs:163) — so if no record of the scene is accepted with t < max_t, the reference returns None.  "true" here is
-// exactly that (under the conservative culling above); "false" decides nothing and the walk runs.
-template <bool COUNT>
-static __device__ __noinline__ bool scene_clear(const SearchScene sc, const V3 o, const V3 d, const double max_t, TraceCount& tc) {
-    const AxisRay ax = make_axis(o.x, d.x, false), ay = make_axis(o.y, d.y, false), az = make_axis(o.z, d.z, false);
-    const CullRay cr = make_cull_ray(sc.cull_o_max, o, d, ax, ay, az);
-    if (!cr.ok || sc.global_root == 0u) return false;
-    const float limit = __double2float_ru(max_t);
-    uint32_t cstk[kMaxCullDepth + 2];
-    int csp = 0;
-    uint32_t cur = sc.global_root - 1u;
-    for (;;) {
-        if (cur & kLeafBit) {
-            double t, u, v;
-            uint32_t id;
-            if (COUNT) tc.mt++;
-            if (moller_trumbore(o, d, sc.tris + (cur & 0x0FFFFFFFu), t, u, v, id) && t < max_t) return false;
-            if (csp == 0) return true;
-            cur = cstk[--csp];
-        } else {
-            const DevCull* __restrict__ c = sc.cull + cur;
-            const float4* bp = reinterpret_cast<const float4*>(c);
-            const float4 f0 = __ldg(bp), f1 = __ldg(bp + 1), f2 = __ldg(bp + 2);
-            const uint2 ch = __ldg(reinterpret_cast<const uint2*>(&c->child[0]));
-            float tn0, tn1;
-            if (COUNT) tc.cull += 2;
-            const bool go0 = cull_box(cr, f0.x, f0.y, f0.z, f0.w, f1.x, f1.y, limit, tn0);
-            const bool go1 = cull_box(cr, f1.z, f1.w, f2.x, f2.y, f2.z, f2.w, limit, tn1);
-            if (go0 && go1) { cstk[csp++] = ch.y; cur = ch.x; }
-            else if (go0 || go1) cur = go0 ? ch.x : ch.y;
-            else if (csp != 0) cur = cstk[--csp];
-            else return true;
-        }
-    }
-}
-
-// (2) Closest-hit rays with max_t = +inf whose origin lies outside the geometry (camera rays).  Let C be the accepted
-// record with the smallest t.  The walk returns C when (proof: DESIGN.md §5.6)
+// (1) `any` — shadow queries (triangle_exists_between_points, raytracer.rs:164-188; DESIGN.md §5.5 "scene_clear").  The
+// walk's result is the minimum-t own hit over the nodes it visits, every one of them a record the exact test ACCEPTS
+// with t < max_t at the root (ray.rs:163) — so if no record of the scene is accepted with t < max_t, the reference
+// returns None: status 1, id kNone (under the conservative culling above).  An accepted record below max_t decides
+// nothing: status 0, and the walk runs.
+//
+// (2) `!any` — closest-hit rays with max_t = +inf whose origin lies outside the geometry (camera rays; DESIGN.md §5.6
+// "sparse_closest").  Let C be the accepted record with the smallest t.  The walk returns C when (proof: DESIGN.md §5.6)
 //   (a) every stored triangle lies inside the box of its node, and the root box is not absurdly larger than the
 //       geometry (flatten: DevScene::sparse_ok);
 //   (b) all three direction components take the fast slab path (finite, non-zero, sane magnitude), the ray is
@@ -448,10 +409,10 @@ static __device__ __noinline__ bool scene_clear(const SearchScene sc, const V3 o
 // visits can beat or tie C.  Anything else: status 0, and the walk runs as if this had not happened.
 constexpr double kSparseWindow = 4.1e-5;   // 2 x (pad 1e-5 + f32 slop 0.6e-5, rounded up to 2e-5) + 2.5 % for roundings
 
-struct SparseResult {
+struct SearchResult {
     double t;
     uint32_t id, rec;
-    uint32_t status;   // 0: handed over; 1: answered (id == kNone: the ray hits nothing)
+    uint32_t status;   // 0: handed over; 1: answered (id == kNone: no record is accepted (below max_t))
 };
 
 // tmin / tmax of reference child k of `pn` with the walk's own arithmetic (slab_axis on the fast path: same operands,
@@ -467,37 +428,29 @@ __device__ __forceinline__ void child_interval(const AxisRay& ax, const AxisRay&
 }
 
 template <bool COUNT>
-static __device__ __noinline__ SparseResult sparse_closest(const SearchScene sc, const V3 o, const V3 d, TraceCount& tc) {
+static __device__ __noinline__ SearchResult scene_search(const SearchScene sc, const V3 o, const V3 d, const double max_t,
+                                                         const bool any, TraceCount& tc) {
     const double kInf = __longlong_as_double(0x7FF0000000000000ll);
-    SparseResult res;
+    SearchResult res;
     res.t = kInf; res.id = kNone; res.rec = 0; res.status = 0u;
-    if (sc.global_root == 0u || sc.sparse_ok == 0u) return res;
+    if (sc.global_root == 0u || (!any && sc.sparse_ok == 0u)) return res;
     const bool ps = sc.planes_safe != 0u;
     const AxisRay ax = make_axis(o.x, d.x, ps), ay = make_axis(o.y, d.y, ps), az = make_axis(o.z, d.z, ps);
     const CullRay cr = make_cull_ray(sc.cull_o_max, o, d, ax, ay, az);
-    if (!cr.ok || !(ax.fast && ay.fast && az.fast)) return res;
+    if (!cr.ok || (!any && !(ax.fast && ay.fast && az.fast))) return res;
     const double ymax = fmax(fmax(fabs(ax.y), fabs(ay.y)), fabs(az.y));
     const double W = kSparseWindow * (sc.cull_o_max * (1.0 / kCullOriginRel)) * ymax;
     double t1 = kInf, t2 = kInf;          // smallest accepted t, and the smallest accepted t of any OTHER record
     uint32_t id1 = kNone, rec1 = 0;
-    float limit = __int_as_float(0x7f800000);
+    float limit = any ? __double2float_ru(max_t) : __int_as_float(0x7f800000);
     uint32_t cstk[kMaxCullDepth + 2];
     int csp = 0;
     uint32_t cur = sc.global_root - 1u;
-    for (;;) {
-        if (cur & kLeafBit) {
-            const uint32_t r = cur & 0x0FFFFFFFu;
-            double t, u, v;
-            uint32_t id;
-            if (COUNT) tc.mt++;
-            if (moller_trumbore(o, d, sc.tris + r, t, u, v, id)) {
-                if (t < t1) { t2 = t1; t1 = t; id1 = id; rec1 = r; }
-                else t2 = min_nn(t2, t);
-                limit = __double2float_ru(t1 + W);     // keep looking a window beyond the best
-            }
-            if (csp == 0) break;
-            cur = cstk[--csp];
-        } else {
+    bool live = true;
+    // rounds of "while inner node / while leaf", nearer child first for both kinds of ray (measured: the order pays for
+    // shadow queries too, profiles/r02_experiments.md)
+    while (live) {
+        while (live && !(cur & kLeafBit)) {
             const DevCull* __restrict__ c = sc.cull + cur;
             const float4* bp = reinterpret_cast<const float4*>(c);
             const float4 f0 = __ldg(bp), f1 = __ldg(bp + 1), f2 = __ldg(bp + 2);
@@ -510,14 +463,30 @@ static __device__ __noinline__ SparseResult sparse_closest(const SearchScene sc,
             if (go0 && go1) { cstk[csp++] = swap ? ch.x : ch.y; cur = swap ? ch.y : ch.x; }
             else if (go0 || go1) cur = go0 ? ch.x : ch.y;
             else if (csp != 0) cur = cstk[--csp];
-            else break;
+            else live = false;
+        }
+        while (live && (cur & kLeafBit)) {
+            const uint32_t r = cur & 0x0FFFFFFFu;
+            double t, u, v;
+            uint32_t id;
+            if (COUNT) tc.mt++;
+            if (moller_trumbore(o, d, sc.tris + r, t, u, v, id)) {
+                if (any) {
+                    if (t < max_t) return res;             // something may be in the way: the walk decides
+                } else {
+                    if (t < t1) { t2 = t1; t1 = t; id1 = id; rec1 = r; }
+                    else t2 = min_nn(t2, t);
+                    limit = __double2float_ru(t1 + W);     // keep looking a window beyond the best
+                }
+            }
+            if (csp != 0) cur = cstk[--csp];
+            else live = false;
         }
     }
-    if (id1 == kNone) { res.status = 1u; return res; }   // no accepted record anywhere: None
-    if (!(t2 > t1 + W)) return res;                      // (c) fails (a NaN anywhere fails it too)
-    // (d): up from C's node
+    if (any || id1 == kNone) { res.status = 1u; return res; }   // no accepted record (below max_t) anywhere: None
+    if (!(t2 > t1 + W)) return res;                              // (c) fails (a NaN anywhere fails it too)
     uint32_t node = __ldg(&sc.tris[rec1].node);
-    while (node != 0u) {
+    while (node != 0u) {                                         // (d): up from C's node
         const DevNode* __restrict__ nd = sc.nodes + node;
         const uint32_t parent = __ldg(&nd->parent), k = __ldg(&nd->child_slot);
         double tmin, tmax;
@@ -531,8 +500,8 @@ static __device__ __noinline__ SparseResult sparse_closest(const SearchScene sc,
 }
 
 // What a caller allows traverse() to try before the walk
-constexpr uint32_t kTryFilter = 1u;   // any-hit rays: scene_clear
-constexpr uint32_t kTrySparse = 2u;   // closest-hit rays with max_t = +inf: sparse_closest
+constexpr uint32_t kTryFilter = 1u;   // any-hit rays: scene_search(any)
+constexpr uint32_t kTrySparse = 2u;   // closest-hit rays with max_t = +inf: scene_search(!any)
 
 // Ray::intersect_with_octant_with_max_t(octree, 0, max_t).  outcome (may be null): 1 = answered by a search,
 // 2 = a search ran and handed the ray to the walk, 0 = walk only.
@@ -542,19 +511,15 @@ __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const 
                                          const uint32_t allow = kTryFilter | kTrySparse, uint32_t* outcome = nullptr) {
     uint32_t oc = 0u;
     bool need_walk = true;
+    const bool try_any = any_hit && (allow & kTryFilter);
+    const bool try_closest = !any_hit && (allow & kTrySparse) && max_t == __longlong_as_double(0x7FF0000000000000ll);
     if (sc.root_tri_count == 0) {
         need_walk = false;   // ray.rs:112-114 at the root
         best.id = kNone; best.rec = 0; best.t = max_t;
-    } else if (any_hit) {
-        if (allow & kTryFilter) {
-            const bool clear = scene_clear<COUNT>(search_scene(sc), o, d, max_t, tc);
-            oc = clear ? 1u : 2u;
-            if (clear) { need_walk = false; best.id = kNone; best.rec = 0; best.t = max_t; }
-        }
-    } else if ((allow & kTrySparse) && max_t == __longlong_as_double(0x7FF0000000000000ll)) {
-        const SparseResult r = sparse_closest<COUNT>(search_scene(sc), o, d, tc);
+    } else if (try_any || try_closest) {
+        const SearchResult r = scene_search<COUNT>(search_scene(sc), o, d, max_t, any_hit, tc);
         oc = r.status ? 1u : 2u;
-        if (r.status) { need_walk = false; best.t = r.t; best.id = r.id; best.rec = r.rec; }
+        if (r.status) { need_walk = false; best.t = any_hit ? max_t : r.t; best.id = r.id; best.rec = r.rec; }
     }
     if (outcome) *outcome = oc;
     if (need_walk) walk<COUNT>(sc, o, d, max_t, any_hit, best, tc);

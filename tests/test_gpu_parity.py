@@ -167,7 +167,7 @@ def test_grazing_rays_the_documented_exception_of_the_culling(rrt, scenes, monke
 
 
 def test_ten_million_random_rays_through_the_searches(rrt, scenes):
-    # the searches of the scene-wide hierarchy (scene_clear / sparse_closest) on 10^7 rays of the
+    # the searches of the scene-wide hierarchy (scene_search: shadow queries / camera rays) on 10^7 rays of the
     # kinds that stress their hand-over rules: camera-like rays from outside, rays from origins INSIDE the geometry
     # (the origin-inside tie rule of ray.rs:49-53), origins exactly on octree planes, zero direction components —
     # closest hit (t, u, v, id) bit for bit against the oracle, on the teapot scene and on a triangle soup

@@ -73,7 +73,7 @@ def emu():
 
 
 # By default the emulation lets traverse() try BOTH searches of the scene-wide hierarchy on every ray they apply to
-# (rrt_trace.cuh: scene_clear on any-hit rays, sparse_closest on closest-hit rays with max_t = inf — also on rays from
+# (rrt_trace.cuh: scene_search on any-hit rays and on closest-hit rays with max_t = inf — also on rays from
 # inside the geometry, which the render kernel leaves to the walk): the whole suite fuzzes their hand-over rules.
 ALLOW_ALL, ALLOW_WALK_ONLY = 3, 0
 
