@@ -16,6 +16,7 @@ namespace rrt {
 
 constexpr uint32_t kNone = 0xFFFFFFFFu;
 constexpr uint32_t kLeafBit = 0x80000000u;  // cull entry: bit31 leaf | (count-1) << 28 | first record
+constexpr uint32_t kDone = 0xFFFFFFFFu;     // bottom of a hierarchy stack: "no entry left" (never a real leaf word, see flatten)
 
 struct TraceCount {
     uint32_t mt = 0, box = 0, cull = 0, nodes = 0;
@@ -196,7 +197,8 @@ __device__ __forceinline__ void walk(const DevScene& sc, const V3& o, const V3& 
     // still have children left are on the stack.  Exhausted levels are never pushed.
     uint2 stk[kMaxOctreeDepth + 1];
     uint32_t lv_first = 0, lv_ord = 0;
-    uint32_t cstk[kMaxCullDepth + 2];  // culling-hierarchy stack (depth bounded by the builder)
+    uint32_t cstk[kMaxCullDepth + 3];  // culling-hierarchy stack (depth bounded by the builder), bottom entry kDone
+    cstk[0] = kDone;
     int sp = 0;
     uint32_t node = 0;
     bool is_root = true;
@@ -226,12 +228,11 @@ __device__ __forceinline__ void walk(const DevScene& sc, const V3& o, const V3& 
         }
         if (scan) {
             uint32_t cur = __ldg(&n->cull_root);
-            int csp = 0;
-            bool live = true;
+            int csp = 1;   // cstk[0] = kDone, see scene_search
             // rounds of "while inner node / while leaf": a lane that reaches a leaf waits for the others of its warp, so
             // the exact tests below run with more lanes than one test per hierarchy step would (profiles/r02_experiments.md)
-            while (live) {
-                while (live && !(cur & kLeafBit)) {
+            while (cur != kDone) {
+                while (!(cur & kLeafBit)) {
                     const DevCull* __restrict__ c = sc.cull + cur;
                     if (COUNT) tc.cull += 2;
                     const float4* bp = reinterpret_cast<const float4*>(c);
@@ -241,18 +242,16 @@ __device__ __forceinline__ void walk(const DevScene& sc, const V3& o, const V3& 
                     const bool go0 = cull_box(cr, f0.x, f0.y, f0.z, f0.w, f1.x, f1.y, limit, tn0);
                     const bool go1 = cull_box(cr, f1.z, f1.w, f2.x, f2.y, f2.z, f2.w, limit, tn1);
                     const bool swap = tn1 < tn0;
-                    if (go0 && go1) {
+                    const bool both = go0 && go1;
+                    uint32_t nxt = go0 ? ch.x : ch.y;
+                    if (both) {
+                        nxt = swap ? ch.y : ch.x;
                         cstk[csp++] = swap ? ch.x : ch.y;
-                        cur = swap ? ch.y : ch.x;
-                    } else if (go0 || go1) {
-                        cur = go0 ? ch.x : ch.y;
-                    } else if (csp != 0) {
-                        cur = cstk[--csp];
-                    } else {
-                        live = false;
                     }
+                    if (!(go0 || go1)) nxt = cstk[--csp];
+                    cur = nxt;
                 }
-                while (live && (cur & kLeafBit)) {
+                while ((cur & kLeafBit) && cur != kDone) {
                     const uint32_t first = cur & 0x0FFFFFFFu;
                     const uint32_t cnt = ((cur >> 28) & 7u) + 1u;
                     bool upd = false;
@@ -262,9 +261,7 @@ __device__ __forceinline__ void walk(const DevScene& sc, const V3& o, const V3& 
                         upd |= test_record(o, d, sc.tris, first + i, nb);
                     }
                     if (upd) limit = __double2float_ru(nb.t);
-                    if (any_hit && nb.id != kNone && nb.t < best.t) live = false;  // best will improve => Some
-                    else if (csp != 0) cur = cstk[--csp];
-                    else live = false;
+                    cur = (any_hit && nb.id != kNone && nb.t < best.t) ? kDone : cstk[--csp];  // best will improve => Some
                 }
             }
         }
@@ -371,21 +368,9 @@ __device__ __forceinline__ void walk(const DevScene& sc, const V3& o, const V3& 
 // flatten builds ONE more culling hierarchy of the usual kind over ALL records of the scene (DevScene::global_root,
 // every leaf a single record): which octree node owns a record does not matter to the two questions below, and a
 // binary SAH hierarchy answers them in ~25 f32 box-pair steps where the walk visits ~10 octree nodes at ~300
-// instructions each.  ONE function answers both (not inlined into the walk: its own register allocation, the walk's
-// code stays small, and a single copy of the loop in the instruction cache; measurements: profiles/r02_experiments.md).
-
-// What the search reads of the scene, handed over BY VALUE: taking the address of the kernel's DevScene parameter for a
-// non-inlined callee would turn every access to it, in the walk too, from a constant-bank operand into a generic load.
-struct SearchScene {
-    const DevNode* nodes;
-    const DevTri* tris;
-    const DevCull* cull;
-    double cull_o_max;
-    uint32_t global_root, sparse_ok, planes_safe, _pad;
-};
-__device__ __forceinline__ SearchScene search_scene(const DevScene& sc) {
-    return SearchScene{sc.nodes, sc.tris, sc.cull, sc.cull_o_max, sc.global_root, sc.sparse_ok, sc.planes_safe, 0u};
-}
+// instructions each.  ONE loop answers both: a single copy in the instruction cache, and both kinds of ray keep a warp
+// converged.  Inlined at traverse()'s one call site: as a called function every trip of the loop re-creates the
+// global-memory descriptor (2 LDC + 4 R2UR), ~9 % of a step (measurements: profiles/r02_experiments.md).
 
 // (1) `any` — shadow queries (triangle_exists_between_points, raytracer.rs:164-188; DESIGN.md §5.5 "scene_clear").  The
 // walk's result is the minimum-t own hit over the nodes it visits, every one of them a record the exact test ACCEPTS
@@ -428,8 +413,8 @@ __device__ __forceinline__ void child_interval(const AxisRay& ax, const AxisRay&
 }
 
 template <bool COUNT>
-static __device__ __noinline__ SearchResult scene_search(const SearchScene sc, const V3 o, const V3 d, const double max_t,
-                                                         const bool any, TraceCount& tc) {
+__device__ __forceinline__ SearchResult scene_search(const DevScene& sc, const V3& o, const V3& d, const double max_t,
+                                                    const bool any, TraceCount& tc) {
     const double kInf = __longlong_as_double(0x7FF0000000000000ll);
     SearchResult res;
     res.t = kInf; res.id = kNone; res.rec = 0; res.status = 0u;
@@ -443,14 +428,16 @@ static __device__ __noinline__ SearchResult scene_search(const SearchScene sc, c
     double t1 = kInf, t2 = kInf;          // smallest accepted t, and the smallest accepted t of any OTHER record
     uint32_t id1 = kNone, rec1 = 0;
     float limit = any ? __double2float_ru(max_t) : __int_as_float(0x7f800000);
-    uint32_t cstk[kMaxCullDepth + 2];
-    int csp = 0;
+    // The stack's bottom entry is kDone (a leaf word no hierarchy holds: flatten keeps record indices below 2^28 - 1), so a
+    // pop needs no emptiness test and "finished" is one more value of `cur` — no flag to carry through the loops.
+    uint32_t cstk[kMaxCullDepth + 3];
+    cstk[0] = kDone;
+    int csp = 1;
     uint32_t cur = sc.global_root - 1u;
-    bool live = true;
     // rounds of "while inner node / while leaf", nearer child first for both kinds of ray (measured: the order pays for
     // shadow queries too, profiles/r02_experiments.md)
-    while (live) {
-        while (live && !(cur & kLeafBit)) {
+    while (cur != kDone) {
+        while (!(cur & kLeafBit)) {
             const DevCull* __restrict__ c = sc.cull + cur;
             const float4* bp = reinterpret_cast<const float4*>(c);
             const float4 f0 = __ldg(bp), f1 = __ldg(bp + 1), f2 = __ldg(bp + 2);
@@ -460,12 +447,16 @@ static __device__ __noinline__ SearchResult scene_search(const SearchScene sc, c
             const bool go0 = cull_box(cr, f0.x, f0.y, f0.z, f0.w, f1.x, f1.y, limit, tn0);
             const bool go1 = cull_box(cr, f1.z, f1.w, f2.x, f2.y, f2.z, f2.w, limit, tn1);
             const bool swap = tn1 < tn0;
-            if (go0 && go1) { cstk[csp++] = swap ? ch.x : ch.y; cur = swap ? ch.y : ch.x; }
-            else if (go0 || go1) cur = go0 ? ch.x : ch.y;
-            else if (csp != 0) cur = cstk[--csp];
-            else live = false;
+            const bool both = go0 && go1;
+            uint32_t nxt = go0 ? ch.x : ch.y;
+            if (both) {
+                nxt = swap ? ch.y : ch.x;
+                cstk[csp++] = swap ? ch.x : ch.y;
+            }
+            if (!(go0 || go1)) nxt = cstk[--csp];
+            cur = nxt;
         }
-        while (live && (cur & kLeafBit)) {
+        while ((cur & kLeafBit) && cur != kDone) {
             const uint32_t r = cur & 0x0FFFFFFFu;
             double t, u, v;
             uint32_t id;
@@ -479,8 +470,7 @@ static __device__ __noinline__ SearchResult scene_search(const SearchScene sc, c
                     limit = __double2float_ru(t1 + W);     // keep looking a window beyond the best
                 }
             }
-            if (csp != 0) cur = cstk[--csp];
-            else live = false;
+            cur = cstk[--csp];
         }
     }
     if (any || id1 == kNone) { res.status = 1u; return res; }   // no accepted record (below max_t) anywhere: None
@@ -517,7 +507,7 @@ __device__ __forceinline__ void traverse(const DevScene& sc, const V3& o, const 
         need_walk = false;   // ray.rs:112-114 at the root
         best.id = kNone; best.rec = 0; best.t = max_t;
     } else if (try_any || try_closest) {
-        const SearchResult r = scene_search<COUNT>(search_scene(sc), o, d, max_t, any_hit, tc);
+        const SearchResult r = scene_search<COUNT>(sc, o, d, max_t, any_hit, tc);
         oc = r.status ? 1u : 2u;
         if (r.status) { need_walk = false; best.t = any_hit ? max_t : r.t; best.id = r.id; best.rec = r.rec; }
     }
