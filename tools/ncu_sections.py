@@ -14,13 +14,18 @@ def line_of(marker):
 
 
 marks = [(1, "trace: min/max helpers"), (line_of("struct AxisRay"), "trace: axis setup / markstein / slab_axis"),
-         (line_of("conservative culling of long lists"), "trace: cull ray + cull_box (f32)"),
+         (line_of("conservative culling in f32"), "trace: cull ray + cull_box (f32, all hierarchies)"),
          (line_of("slab_hit_bit(double"), "trace: child hit predicate"),
-         (line_of("bool test_record"), "trace: test_record"), (line_of("void traverse("), "trace: traverse set-up"),
-         (line_of("---- own triangles"), "trace: node header + list box"), (line_of("while (live)"), "trace: cull loop (inner nodes)"),
-         (line_of("if (was_leaf)"), "trace: leaf records loop"), (line_of("---- children"), "trace: children planes + slabs"),
-         (line_of("double nxy"), "trace: children tmin/tmax/key/hit"), (line_of("as repeated selection of the smallest"), "trace: child sort + push"),
-         (line_of("---- next node"), "trace: pop next node")]
+         (line_of("bool test_record"), "trace: test_record"), (line_of("void walk("), "walk: set-up"),
+         (line_of("---- own triangles"), "walk: node header + list hierarchy + leaf records"),
+         (line_of("---- children"), "walk: children planes + slabs"),
+         (line_of("double nxy"), "walk: children tmin/tmax/key/hit + subtree boxes"),
+         (line_of("as repeated selection of the smallest"), "walk: child sort + push"),
+         (line_of("---- next node"), "walk: pop next node"),
+         (line_of("void child_interval("), "search: way up (child_interval)"),
+         (line_of("SearchResult scene_search("), "search: set-up + hierarchy steps + leaf bookkeeping"),
+         (line_of("(d): up from"), "search: way up (child_interval)"),
+         (line_of("void traverse("), "trace: traverse dispatch")]
 
 
 def section(f, l):
