@@ -183,7 +183,10 @@ int rrt_scene_search_state(rrt_scene* scene, uint32_t out[12]);
  * (0x00RRGGBB, row-major, top row first, row 0 left zero: engine.rs:146-158, entities.rs:32-36).
  * hit_ids (may be NULL): int32[height][width][4], depth-0 hit triangle per supersample in the order
  * d1..d4 of engine.rs:207-236, -1 = miss / row 0.  device_ms (may be NULL) = kernel time (CUDA events).
- * Synchronous; includes the device->host copy. */
+ * Synchronous: the frame is in fb_0rgb on return.  When fb_0rgb is PAGE-LOCKED host memory (cudaHostAlloc,
+ * cudaHostRegister, rrt_host_frame_pin) the render kernel stores every finished pixel straight into it over PCIe while
+ * the frame is being rendered and no device->host copy follows; pageable memory gets render + copy.  Same frame either
+ * way (RRT_HOST_STORES=0 forces the copy). */
 int rrt_render(rrt_scene* scene, const rrt_render_params* params,
                uint32_t* fb_0rgb, int32_t* hit_ids, float* device_ms);
 
@@ -261,7 +264,8 @@ int rrt_host_frame_fetch_handle(rrt_host_frame* f, double timeout_s, unsigned ch
 void rrt_host_frame_close(rrt_host_frame* f);                /* the creator also unlinks the segment */
 /* Renders the shard (as rrt_render_device) and enqueues the copy of its rows to their places in the FULL host frame
  * `host_frame` (width*height words; rrt_host_frame_pixels() or any caller buffer, asynchronous if page-locked) on
- * `cuda_stream`; does not synchronise.  With n_shards = 1 this is rrt_render without the blocking copy. */
+ * `cuda_stream`; does not synchronise.  With n_shards = 1 this is rrt_render without the blocking copy.  A page-locked
+ * host_frame takes the kernel's pixels directly (see rrt_render): nothing but the kernel is enqueued. */
 int rrt_render_to_host_frame(rrt_scene* scene, const rrt_render_params* params, const rrt_shard* shard,
                              uint32_t* host_frame, void* cuda_stream);
 

@@ -239,6 +239,34 @@ def test_host_frame_single_rank_equals_rrt_render(rrt, scenes):
     rt.close()
 
 
+def test_page_locked_host_buffers_take_direct_stores_and_give_the_same_frame(rrt, scenes):
+    # A page-locked caller buffer is written by the render kernel itself (posted PCIe stores, no device->host copy:
+    # host_frame_alias in csrc/rrt_api.cu); a pageable one goes through render + copy.  Same frame either way, for
+    # rrt_render and for the shards of rrt_render_to_host_frame, including buffers at an offset inside a pinned block.
+    import torch
+    sd = scenes("model2")
+    rt = rrt.RayTracer(sd)
+    L = rrt.abi.lib()
+    for W, H, G, T in ((320, 180, 1, 8), (333, 101, 3, 8)):
+        p = rt.params(W, H)
+        pageable = np.full((H, W), 0xDEADBEEF, dtype=np.uint32)
+        rrt.abi.check(L.rrt_render(rt.handle, C.byref(p), pageable.ctypes.data_as(C.c_void_p), None, None))
+        block = torch.full((H * W + 64,), -1, dtype=torch.int32, pin_memory=True)
+        pinned = block[37:37 + H * W]                       # not at the start of the allocation
+        rrt.abi.check(L.rrt_render(rt.handle, C.byref(p), C.c_void_p(pinned.data_ptr()), None, None))
+        assert np.array_equal(pinned.numpy().view(np.uint32).reshape(H, W), pageable), (W, H)
+        assert (block[:37] == -1).all() and (block[37 + H * W:] == -1).all()    # nothing outside the frame was touched
+        for host in (torch.zeros((H, W), dtype=torch.int32, pin_memory=True), np.zeros((H, W), dtype=np.uint32)):
+            ptr = host.data_ptr() if hasattr(host, "data_ptr") else host.ctypes.data
+            for r in range(G):
+                sh = rrt.abi.Shard(T, G, r)
+                rrt.abi.check(L.rrt_render_to_host_frame(rt.handle, C.byref(p), C.byref(sh), C.c_void_p(ptr), None))
+                torch.cuda.synchronize()
+            got = host.numpy().view(np.uint32) if hasattr(host, "data_ptr") else host
+            assert np.array_equal(got, pageable), (W, H, G, T, type(host))
+    rt.close()
+
+
 def test_order_hint_changes_nothing(rrt, scenes):
     # rrt_scene_order_hint: from the second frame of a shape on, the last part of the frame's 16x4-pixel blocks is
     # handed out heaviest first (cost measured during the previous frame, sorted on a side stream).  Only the ORDER
