@@ -437,8 +437,10 @@ def run_gpu(args):
             "clocks": clocks,
             "e2e": {"value": e2e_val, "unit": "Mrays/s", "h2d_bytes_per_step": C.sizeof(abi.RenderParams),
                     "d2h_bytes_per_step": W * H * 4, "ms_per_step": float(e2e_ms.item()) / K,
-                    "path": "Scene.draw_scene -> rrt_render (pinned host canvas)" if world == 1 else
-                            "ShardedRenderer(assemble='host'): rrt_render_to_host_frame per rank + rrt_host_frame_barrier"},
+                    "path": ("Scene.draw_scene -> rrt_render (pinned host canvas" if world == 1 else
+                             "ShardedRenderer(assemble='host'): rrt_render_to_host_frame per rank + rrt_host_frame_barrier (shared pinned canvas")
+                            + ("; the render kernel stores the finished pixels into it over PCIe: d2h bytes = those stores)"
+                               if os.environ.get("RRT_HOST_STORES", "1") != "0" else "; render into device memory, then copy)")},
             # steady state vs what a one-shot caller sees: first frame of a handle at this shape (raster order, both searches
             # tried), and the K timed frames again with the dispatch-order hint switched off
             "first_frame_ms": first_ms, "ms_per_step_no_hint": nohint_ms,

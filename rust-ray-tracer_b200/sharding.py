@@ -89,10 +89,12 @@ class ShardedRenderer:
         frame k, so by the time any rank stores frame k+2 into the buffer of frame k that consumer has run.
         Rule for the caller: consume `frame` on the render stream (or make that stream wait for the consumer)
         before calling render() again.
-    assemble="host": the frame is wanted in HOST memory (the reference's Canvas.buffer, engine.rs:123-128): every
-        rank renders compactly and copies ITS rows over its own PCIe link into one page-locked shared-memory
-        frame (HostFrame); assemble() = a barrier ("rank 0 is done reading the previous frame", waited for while the
-        kernel runs), the copy, a stream sync and a second barrier ("frame complete").  No device-side exchange at all.
+    assemble="host": the frame is wanted in HOST memory (the reference's Canvas.buffer, engine.rs:123-128), in one
+        page-locked shared-memory frame (HostFrame) that every rank maps.  Default: every rank's render kernel stores
+        the pixels of ITS rows straight into that frame over its own PCIe link (rrt_render_to_host_frame); render() first
+        waits for "rank 0 is done reading the previous frame", assemble() = a stream sync and the barrier "frame
+        complete".  With RRT_HOST_STORES=0: render compactly into device memory, then (behind the first barrier, which
+        then hides behind the kernel) copy the rows out.  No device-side exchange at all either way.
     """
 
     def __init__(self, ray_tracer, width, height, rank, world, tile_rows=DEFAULT_TILE_ROWS, group=None,
@@ -110,6 +112,8 @@ class ShardedRenderer:
         self._own_frames, self._peer_frames, self._host = [], [], None
         self._k = 0                 # frames rendered so far (peer: selects the buffer)
         self._outstanding = False   # host: a completed frame has not been released yet
+        import os
+        self._direct = os.environ.get("RRT_HOST_STORES", "1") != "0"   # host: kernels store into the canvas themselves
         if self.mode == "peer":
             self._setup_peer_frames()
             return
@@ -190,6 +194,14 @@ class ShardedRenderer:
                                                              C.c_void_p(self._dest[self._cur]), C.c_void_p(s.cuda_stream)))
             return
         if self.mode == "host":
+            if self._direct:
+                # the kernel stores its pixels straight into the shared page-locked canvas (rrt_render_to_host_frame,
+                # direct host stores): it may only start once rank 0 has finished reading the previous frame
+                if self._outstanding and self.world > 1:
+                    self._host.barrier()
+                abi.check(abi.lib().rrt_render_to_host_frame(self.rt.handle, C.byref(params), C.byref(self.shard),
+                                                             C.c_void_p(self._host.ptr), C.c_void_p(s.cuda_stream)))
+                return
             # render first; "rank 0 has finished reading the previous frame" is only needed before the COPY (assemble)
             abi.check(abi.lib().rrt_render_device(self.rt.handle, C.byref(params), C.byref(self.shard),
                                                   self._rows.data_ptr(), None, C.c_void_p(s.cuda_stream)))
@@ -206,11 +218,12 @@ class ShardedRenderer:
         import torch.distributed as dist
         s = stream or torch.cuda.current_stream(self.device)
         if self.mode == "host":
-            if self._outstanding and self.world > 1:
-                self._host.barrier()          # rank 0 has finished reading the previous frame (waited for behind the kernel)
-            abi.check(abi.lib().rrt_copy_shard_to_host_frame(self.rt.device, self._rows.data_ptr(), self.W, self.H,
-                                                             C.byref(self.shard), C.c_void_p(self._host.ptr),
-                                                             C.c_void_p(s.cuda_stream)))
+            if not self._direct:
+                if self._outstanding and self.world > 1:
+                    self._host.barrier()      # rank 0 has finished reading the previous frame (waited for behind the kernel)
+                abi.check(abi.lib().rrt_copy_shard_to_host_frame(self.rt.device, self._rows.data_ptr(), self.W, self.H,
+                                                                 C.byref(self.shard), C.c_void_p(self._host.ptr),
+                                                                 C.c_void_p(s.cuda_stream)))
             s.synchronize()
             if self.world > 1:
                 self._host.barrier()          # every rank's rows have landed: the frame is complete
