@@ -195,7 +195,8 @@ int rrt_render(rrt_scene* scene, const rrt_render_params* params,
  * layout as rrt_render; pinned host memory makes the copies asynchronous) WHILE frame i+1 renders — two device
  * frames, a render stream and a copy stream inside the handle.  Synchronous: returns when the last frame is in
  * host memory.  total_ms (may be NULL) = device time from the first kernel to the last copy.
- * Each frame is what rrt_render produces for the same params. */
+ * Each frame is what rrt_render produces for the same params.  Page-locked fbs[i] take the kernel's pixels directly
+ * (see rrt_render): no copy stage at all for those frames. */
 int rrt_render_frames(rrt_scene* scene, const rrt_render_params* params, int32_t n_frames,
                       uint32_t* const* fbs, float* total_ms);
 

@@ -598,8 +598,16 @@ int rrt_render_frames(rrt_scene* s, const rrt_render_params* params, int32_t n_f
             if ((rc = make_params(s, params + i, nullptr, &P))) return rc;
             const size_t n = (size_t)P.W * P.H;
             const int b = i & 1;
-            if ((rc = ensure(&s->d_seq_fb[b], &s->seq_cap[b], n))) return rc;   // no-op after the first two frames
             if ((rc = ensure(&s->d_scratch, &s->scratch_cap, render_scratch_words(P.n_rows_local, P.W)))) return rc;
+            if (uint32_t* alias = host_frame_alias(fbs[i], n)) {
+                // page-locked destination: the kernel stores frame i into it itself; nothing to copy, nothing to wait for
+                CU(render_frame(s, P, alias, nullptr, nullptr, s->seq_render));
+                CU(cudaEventRecord(s->seq_rendered[b], s->seq_render));
+                CU(cudaStreamWaitEvent(s->seq_copy, s->seq_rendered[b], 0));   // keeps seq_t1 (on the copy stream) behind it
+                CU(cudaEventRecord(s->seq_copied[b], s->seq_copy));
+                continue;
+            }
+            if ((rc = ensure(&s->d_seq_fb[b], &s->seq_cap[b], n))) return rc;   // no-op after the first two frames
             if (i >= 2) CU(cudaStreamWaitEvent(s->seq_render, s->seq_copied[b], 0));   // frame i-2 has left this buffer
             CU(render_frame(s, P, s->d_seq_fb[b], nullptr, nullptr, s->seq_render));
             CU(cudaEventRecord(s->seq_rendered[b], s->seq_render));
