@@ -164,6 +164,13 @@ int rrt_scene_get_stats(const rrt_scene* scene, rrt_scene_stats* out);
  * on one stream at a time (they share the handle's scratch and this state). */
 int rrt_scene_order_hint(rrt_scene* scene, int enable);
 
+/* Optional, once per frame shape: allocates NOW what the first render call of this shape (resolution + shard, NULL =
+ * whole frame) would otherwise allocate inside that call — the per-pixel accumulators, the arrays of the dispatch-order
+ * hint, and with_device_frame != 0 the device frame of the copy path (pageable host buffers) — so that the first frame
+ * costs what a frame costs.  The analogue of Canvas::new(width, height) allocating the buffer before draw_scene
+ * (src/scene/engine.rs:123-128, src/main.rs:59-62).  Render calls of other shapes still work (they re-allocate). */
+int rrt_scene_reserve(rrt_scene* scene, const rrt_render_params* params, const rrt_shard* shard, int with_device_frame);
+
 /* Searches that go round the octree walk (no counterpart in the reference; results are bit-identical in every mode).
  * Scene creation also builds ONE culling hierarchy over all triangles of the scene; shadow queries first ask it whether
  * any triangle is hit below max_t at all ("none" is exactly the reference's None), camera rays look for their closest

@@ -79,7 +79,7 @@ SYMBOLS = [
     "rrt_abi_version", "rrt_last_error", "rrt_device_count", "rrt_render_params_default",
     "rrt_scene_create", "rrt_scene_destroy", "rrt_scene_get_stats", "rrt_scene_order_hint",
     "rrt_scene_search_mode", "rrt_scene_search_state",
-    "rrt_render", "rrt_render_frames", "rrt_render_device", "rrt_render_device_noalloc", "rrt_shard_rows", "rrt_deinterleave_device",
+    "rrt_scene_reserve", "rrt_render", "rrt_render_frames", "rrt_render_device", "rrt_render_device_noalloc", "rrt_shard_rows", "rrt_deinterleave_device",
     "rrt_render_device_into_frame", "rrt_frame_alloc", "rrt_frame_free", "rrt_ipc_get_handle", "rrt_ipc_open_handle",
     "rrt_ipc_close_handle", "rrt_copy_frame_to_host",
     "rrt_host_frame_create", "rrt_host_frame_open", "rrt_host_frame_pixels", "rrt_host_frame_geometry",
@@ -118,6 +118,7 @@ def lib():
     L.rrt_scene_order_hint.argtypes = [vp, C.c_int]
     L.rrt_scene_search_mode.argtypes = [vp, C.c_int, C.c_int, C.c_int]
     L.rrt_scene_search_state.argtypes = [vp, C.POINTER(C.c_uint32)]
+    L.rrt_scene_reserve.argtypes = [vp, C.POINTER(RenderParams), C.POINTER(Shard), C.c_int]
     L.rrt_render.argtypes = [vp, C.POINTER(RenderParams), vp, vp, C.POINTER(C.c_float)]
     L.rrt_render_frames.argtypes = [vp, C.POINTER(RenderParams), C.c_int32, C.POINTER(vp), C.POINTER(C.c_float)]
     L.rrt_render_device.argtypes = [vp, C.POINTER(RenderParams), C.POINTER(Shard), vp, vp, vp]

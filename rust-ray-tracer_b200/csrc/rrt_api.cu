@@ -420,6 +420,19 @@ int rrt_render_device_noalloc(rrt_scene* s, const rrt_render_params* p, const rr
     return RRT_OK;
 }
 
+int rrt_scene_reserve(rrt_scene* s, const rrt_render_params* p, const rrt_shard* shard, int with_device_frame) {
+    if (!s) return fail(RRT_ERR_INVALID, "null scene");
+    DevParams P;
+    int rc = make_params(s, p, shard, &P);
+    if (rc) return rc;
+    CU(cudaSetDevice(s->device));
+    if ((rc = ensure(&s->d_scratch, &s->scratch_cap, render_scratch_words(P.n_rows_local, P.W)))) return rc;
+    if (with_device_frame && (rc = ensure(&s->d_fb, &s->fb_cap, (size_t)P.W * std::max(P.n_rows_local, 1)))) return rc;
+    CU(reserve_render(P, &s->sched, 0));
+    CU(cudaStreamSynchronize(0));
+    return RRT_OK;
+}
+
 int rrt_render_device_into_frame(rrt_scene* s, const rrt_render_params* p, const rrt_shard* shard, uint32_t* d_frame,
                                  void* cuda_stream) {
     if (!s || !d_frame) return fail(RRT_ERR_INVALID, "null argument");

@@ -310,29 +310,36 @@ void RenderSchedule::release() {
     cap_blocks = 0; temp_bytes = 0; valid = false; pending = false;
 }
 
+// The schedule's arrays, streams and events for frames of up to n_blocks blocks (no-op when they are there already).
+static cudaError_t schedule_allocate(RenderSchedule* sch, uint32_t n_blocks, cudaStream_t stream) {
+    if (n_blocks <= sch->cap_blocks && sch->order) return cudaSuccess;
+    cudaError_t e;
+    sch->release();
+    if ((e = cudaStreamCreateWithFlags(&sch->side, cudaStreamNonBlocking)) != cudaSuccess) return e;
+    if ((e = cudaEventCreateWithFlags(&sch->ev_rendered, cudaEventDisableTiming)) != cudaSuccess) return e;
+    if ((e = cudaEventCreateWithFlags(&sch->ev_sorted, cudaEventDisableTiming)) != cudaSuccess) return e;
+    uint32_t** bufs[] = {&sch->order, &sch->cost, &sch->keys, &sch->keys_alt, &sch->iota};
+    for (uint32_t** b : bufs)
+        if ((e = cudaMalloc((void**)b, (size_t)n_blocks * sizeof(uint32_t))) != cudaSuccess) return e;
+    size_t bytes = 0;
+    if ((e = cub::DeviceRadixSort::SortPairsDescending(nullptr, bytes, sch->keys, sch->keys_alt, sch->iota, sch->order,
+                                                       (int)n_blocks, 0, 6, stream)) != cudaSuccess) return e;
+    if ((e = cudaMalloc(&sch->temp, bytes ? bytes : 1)) != cudaSuccess) return e;
+    if ((e = cudaMalloc((void**)&sch->stats, 4 * sizeof(unsigned long long))) != cudaSuccess) return e;
+    sch->temp_bytes = bytes;
+    sch->cap_blocks = n_blocks;
+    sch->n_blocks = 0;   // no shape yet: the next launch arms the cost array
+    iota_kernel<<<(n_blocks + 255u) / 256u, 256, 0, stream>>>(sch->iota, n_blocks);
+    return cudaGetLastError();
+}
+
 // Make the schedule fit this launch; a launch of another shape (resolution, shard) starts from raster order again.
 static cudaError_t schedule_prepare(RenderSchedule* sch, const DevParams& P, uint32_t n_blocks, cudaStream_t stream) {
     const bool same = sch->n_blocks == n_blocks && sch->W == P.W && sch->rows == P.n_rows_local && sch->n_shards == P.n_shards &&
                       sch->shard_index == P.shard_index && sch->tile_rows == P.tile_rows;
     if (same && sch->order) return cudaSuccess;
     cudaError_t e;
-    if (n_blocks > sch->cap_blocks || !sch->order) {
-        sch->release();
-        if ((e = cudaStreamCreateWithFlags(&sch->side, cudaStreamNonBlocking)) != cudaSuccess) return e;
-        if ((e = cudaEventCreateWithFlags(&sch->ev_rendered, cudaEventDisableTiming)) != cudaSuccess) return e;
-        if ((e = cudaEventCreateWithFlags(&sch->ev_sorted, cudaEventDisableTiming)) != cudaSuccess) return e;
-        uint32_t** bufs[] = {&sch->order, &sch->cost, &sch->keys, &sch->keys_alt, &sch->iota};
-        for (uint32_t** b : bufs)
-            if ((e = cudaMalloc((void**)b, (size_t)n_blocks * sizeof(uint32_t))) != cudaSuccess) return e;
-        size_t bytes = 0;
-        if ((e = cub::DeviceRadixSort::SortPairsDescending(nullptr, bytes, sch->keys, sch->keys_alt, sch->iota, sch->order,
-                                                           (int)n_blocks, 0, 6, stream)) != cudaSuccess) return e;
-        if ((e = cudaMalloc(&sch->temp, bytes ? bytes : 1)) != cudaSuccess) return e;
-        if ((e = cudaMalloc((void**)&sch->stats, 4 * sizeof(unsigned long long))) != cudaSuccess) return e;
-        sch->temp_bytes = bytes;
-        sch->cap_blocks = n_blocks;
-        iota_kernel<<<(n_blocks + 255u) / 256u, 256, 0, stream>>>(sch->iota, n_blocks);
-    }
+    if ((e = schedule_allocate(sch, n_blocks, stream)) != cudaSuccess) return e;
     if ((e = cudaMemsetAsync(sch->cost, 0, (size_t)n_blocks * sizeof(uint32_t), stream)) != cudaSuccess) return e;
     if ((e = cudaMemsetAsync(sch->stats, 0, 4 * sizeof(unsigned long long), stream)) != cudaSuccess) return e;
     sch->n_blocks = n_blocks; sch->W = P.W; sch->rows = P.n_rows_local; sch->n_shards = P.n_shards;
@@ -428,6 +435,24 @@ cudaError_t launch_render(const DevScene& sc, const DevParams& P, uint32_t* d_fb
         sch->valid = true;
     }
     return cudaGetLastError();
+}
+
+// Everything launch_render would otherwise set up inside the FIRST frame of shape P (rrt_scene_reserve): the schedule's
+// arrays, side stream and events, and the occupancy queries of the kernel variants.
+cudaError_t reserve_render(const DevParams& P, RenderSchedule* sch, cudaStream_t stream) {
+    int n_sm = 0, per_sm = 0;
+    cudaError_t e;
+    for (int which = 0; which < 2; ++which)
+        if ((e = render_occupancy(which, &n_sm, &per_sm)) != cudaSuccess) return e;
+    const uint32_t tiles_x = (uint32_t)((P.W + kTileW - 1) / kTileW), tiles_y = (uint32_t)((P.n_rows_local + kTileH - 1) / kTileH);
+    const uint32_t n_blocks = tiles_x * tiles_y;
+    if (!sch || !sch->enabled || n_blocks < sch->min_blocks) return cudaSuccess;
+    if (schedule_allocate(sch, n_blocks, stream) != cudaSuccess) {   // as in launch_render: no memory, no hint
+        (void)cudaGetLastError();
+        sch->release();
+        sch->enabled = false;
+    }
+    return cudaSuccess;
 }
 
 #if RRT_TIMELINE

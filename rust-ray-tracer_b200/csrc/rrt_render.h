@@ -35,6 +35,8 @@ struct RenderSchedule {
 cudaError_t launch_render(const DevScene& sc, const DevParams& P, uint32_t* d_fb, int32_t* d_hit, uint32_t* d_scratch,
                           DevCounters* d_counters, cudaStream_t stream, RenderSchedule* sch = nullptr);
 size_t render_scratch_words(int n_rows_local, int W);
+// what launch_render would set up inside the first frame of shape P (schedule arrays, occupancy queries), done ahead
+cudaError_t reserve_render(const DevParams& P, RenderSchedule* sch, cudaStream_t stream);
 // Allocation-free variant (rrt_render_device_noalloc): scratch in a static device array of rrt_render.cu, at most
 // kNoAllocMaxPixels pixels per call (cudaErrorInvalidValue beyond), no dispatch-order hint.
 constexpr uint32_t kNoAllocMaxPixels = 1u << 21;   // == RRT_NOALLOC_MAX_PIXELS (include/rrt.h): 2 Mi pixels, 8 MiB of scratch

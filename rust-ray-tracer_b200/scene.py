@@ -234,6 +234,11 @@ class Scene:
         self.hit_ids = None
         self.device_ms = None
 
+    def reserve(self, rt: RayTracer):
+        """Allocate now what the first draw_scene of this canvas size would allocate inside the call (rrt_scene_reserve)."""
+        p = rt.params(self.canvas.width, self.canvas.height)
+        abi.check(abi.lib().rrt_scene_reserve(rt.handle, C.byref(p), None, 1))
+
     def draw_scene(self, rt: RayTracer, want_hit_ids=False, **param_overrides):
         W, H = self.canvas.width, self.canvas.height
         p = rt.params(W, H, **param_overrides)

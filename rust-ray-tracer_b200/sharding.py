@@ -114,6 +114,10 @@ class ShardedRenderer:
         self._outstanding = False   # host: a completed frame has not been released yet
         import os
         self._direct = os.environ.get("RRT_HOST_STORES", "1") != "0"   # host: kernels store into the canvas themselves
+        # set-up, not first-frame work: the accumulators and the dispatch-order arrays of this shape (rrt_scene_reserve)
+        p0 = ray_tracer.params(width, height)
+        abi.check(abi.lib().rrt_scene_reserve(ray_tracer.handle, C.byref(p0), C.byref(self.shard),
+                                              1 if (self.mode == "host" and not self._direct) else 0))
         if self.mode == "peer":
             self._setup_peer_frames()
             return

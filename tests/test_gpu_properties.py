@@ -267,6 +267,29 @@ def test_page_locked_host_buffers_take_direct_stores_and_give_the_same_frame(rrt
     rt.close()
 
 
+def test_reserve_changes_nothing_but_where_the_allocation_happens(rrt, scenes):
+    # rrt_scene_reserve: the first frame of a reserved shape, of a smaller and of a LARGER shape than reserved, whole
+    # and sharded — always the frame an unreserved handle renders
+    sd = scenes("model2")
+    plain, res = rrt.RayTracer(sd), rrt.RayTracer(sd)
+    L = rrt.abi.lib()
+    p0 = res.params(640, 360)
+    rrt.abi.check(L.rrt_scene_reserve(res.handle, C.byref(p0), None, 1))
+    sh = rrt.abi.Shard(8, 3, 1)
+    rrt.abi.check(L.rrt_scene_reserve(res.handle, C.byref(p0), C.byref(sh), 0))
+    for W, H in ((640, 360), (320, 200), (1280, 720), (640, 360)):
+        a = rrt.Scene(W, H).draw_scene(plain).copy()
+        sc = rrt.Scene(W, H)
+        if (W, H) == (1280, 720):
+            sc.reserve(res)
+        assert np.array_equal(sc.draw_scene(res), a), (W, H)
+    bad = res.params(640, 360)
+    bad.max_depth = 99
+    assert L.rrt_scene_reserve(res.handle, C.byref(bad), None, 0) != 0      # same argument checks as a render call
+    plain.close()
+    res.close()
+
+
 def test_order_hint_changes_nothing(rrt, scenes):
     # rrt_scene_order_hint: from the second frame of a shape on, the last part of the frame's 16x4-pixel blocks is
     # handed out heaviest first (cost measured during the previous frame, sorted on a side stream).  Only the ORDER
