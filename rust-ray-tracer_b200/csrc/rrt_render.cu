@@ -376,6 +376,18 @@ static cudaError_t render_occupancy(int which, int* n_sm, int* per_sm) {
     return cudaSuccess;
 }
 
+// cost[] -> order[] on stream `st`: {sum, max}, sort keys (which also clears cost[] for the next recording), one stable
+// 6-bit radix sort of the block ids.
+static cudaError_t schedule_update(RenderSchedule* sch, uint32_t n_blocks, float resident_warps, cudaStream_t st) {
+    unsigned long long* stats = sch->stats + 2 * (sch->parity & 1);
+    order_stats_kernel<<<(n_blocks + 1023u) / 1024u, 256, 0, st>>>(sch->cost, n_blocks, stats);
+    order_keys_kernel<<<(n_blocks + 255u) / 256u, 256, 0, st>>>(sch->cost, sch->keys, n_blocks, stats,
+                                                                sch->stats + 2 * (~sch->parity & 1), resident_warps, sch->tail_safety);
+    sch->parity ^= 1;
+    return cub::DeviceRadixSort::SortPairsDescending(sch->temp, sch->temp_bytes, sch->keys, sch->keys_alt, sch->iota, sch->order,
+                                                     (int)n_blocks, 0, 6, st);
+}
+
 // scratch = (n_rows_local*W + 2) u32 words: per-pixel accumulators followed by the 64-bit queue head.
 cudaError_t launch_render(const DevScene& sc, const DevParams& P, uint32_t* d_fb, int32_t* d_hit, uint32_t* d_scratch,
                           DevCounters* d_counters, cudaStream_t stream, RenderSchedule* sch) {
@@ -408,7 +420,6 @@ cudaError_t launch_render(const DevScene& sc, const DevParams& P, uint32_t* d_fb
     const unsigned grid = (unsigned)(want < resident ? want : resident);
     const uint32_t* order = hint && sch->valid ? sch->order : nullptr;
     uint32_t* cost = hint ? sch->cost : nullptr;
-    unsigned long long* stats = hint ? sch->stats + 2 * (sch->parity & 1) : nullptr;
     if (d_counters)
         render_kernel<true, false><<<grid, kBlock, 0, stream>>>(sc, P, d_fb, d_hit, d_scratch, next, d_counters, tiles_x, total, nullptr, nullptr);
     else if (hint)
@@ -423,13 +434,7 @@ cudaError_t launch_render(const DevScene& sc, const DevParams& P, uint32_t* d_fb
         cudaStream_t side = sch->side;
         if ((e = cudaEventRecord(sch->ev_rendered, stream)) != cudaSuccess) return e;
         if ((e = cudaStreamWaitEvent(side, sch->ev_rendered, 0)) != cudaSuccess) return e;
-        order_stats_kernel<<<(n_blocks + 1023u) / 1024u, 256, 0, side>>>(sch->cost, n_blocks, stats);
-        order_keys_kernel<<<(n_blocks + 255u) / 256u, 256, 0, side>>>(sch->cost, sch->keys, n_blocks, stats,
-                                                                      sch->stats + 2 * (~sch->parity & 1),
-                                                                      (float)grid * (kBlock / 32), sch->tail_safety);
-        sch->parity ^= 1;
-        if ((e = cub::DeviceRadixSort::SortPairsDescending(sch->temp, sch->temp_bytes, sch->keys, sch->keys_alt, sch->iota,
-                                                           sch->order, (int)n_blocks, 0, 6, side)) != cudaSuccess) return e;
+        if ((e = schedule_update(sch, n_blocks, (float)grid * (kBlock / 32), side)) != cudaSuccess) return e;
         if ((e = cudaEventRecord(sch->ev_sorted, side)) != cudaSuccess) return e;
         sch->pending = true;
         sch->valid = true;
