@@ -69,6 +69,8 @@ pub fn draw_scene(&mut self, rt: RayTracer) {
         }
         let mut scene: *mut rrt_scene = std::ptr::null_mut();
         if rrt_scene_create(&desc, 0, &mut scene) != 0 { panic!("rrt_scene_create: {}", last_error()); }
+        // canvas.buffer is a pageable Vec<u32>: rrt_render renders into device memory and copies.  Page-lock it once
+        // (cudaHostRegister on buffer.as_ptr(), outside this function) and the kernel stores the pixels into it directly.
         let rc = rrt_render(scene, &p, self.canvas.buffer.as_mut_ptr(), std::ptr::null_mut(), std::ptr::null_mut());
         rrt_scene_destroy(scene);
         if rc != 0 { panic!("rrt_render: {}", last_error()); }

@@ -50,6 +50,9 @@ extern "C" {
     pub fn rrt_scene_create(desc: *const rrt_scene_desc, device: c_int, out: *mut *mut rrt_scene) -> c_int;
     pub fn rrt_scene_destroy(scene: *mut rrt_scene);
     pub fn rrt_scene_order_hint(scene: *mut rrt_scene, enable: c_int) -> c_int;
+    /// optional, once per frame size: allocate at set-up what the first rrt_render of that size would allocate inside the call
+    pub fn rrt_scene_reserve(scene: *mut rrt_scene, params: *const rrt_render_params, shard: *const rrt_shard,
+                             with_device_frame: c_int) -> c_int;
     pub fn rrt_render(scene: *mut rrt_scene, params: *const rrt_render_params, fb_0rgb: *mut u32,
                       hit_ids: *mut i32, device_ms: *mut f32) -> c_int;
     pub fn rrt_render_frames(scene: *mut rrt_scene, params: *const rrt_render_params, n_frames: i32,
