@@ -179,7 +179,8 @@ def kernel_id():
 def roofline_block(prof, w, kern_ms, have_prof, kid, fp64_peak, hbm_peak, hbm_src, clocks, n_sm):
     """The `roofline` object of the JSON line.  Every count comes from the committed ncu capture of workload `w`
     (profiles/traffic.json, written by tools/ncu_digest.py); every time and peak is measured in this run.  Without a
-    capture of this workload (or at N > 1, where one launch covers a shard) the fractions are null, never a guess."""
+    capture of this workload (or at N > 1, where one launch covers a shard; or on c5, whose timed orbit frames are not
+    the captured frame) the fractions are null, never a guess."""
     sec = kern_ms * 1e-3
     warp_inst, lane_inst, traffic = prof.get(w + "_warp_inst"), prof.get(w + "_fp64_lane_inst"), prof.get(w)
     mhz = (clocks or {}).get("sm_mhz") or (clocks or {}).get("sm_max_mhz") or 1965.0
@@ -412,7 +413,9 @@ def run_gpu(args):
             pass
         w = args.workload
         kid = kernel_id()
-        have_prof = world == 1 and (w + "_fp64_lane_inst") in prof
+        # c5 walks the orbit: the timed frames are other frames than the captured one (frame 0, searches still on), so
+        # a count from that capture over these frames' time would be a guess -> null fractions, ncu percentages only
+        have_prof = world == 1 and w != "c5" and (w + "_fp64_lane_inst") in prof
         order_hint = os.environ.get("RRT_ORDER_HINT", "1") != "0"
         line = {
             "metric": "Mrays/s (primary rays, 4 per pixel)", "value": value, "unit": "Mrays/s", "n_gpus": world,
